@@ -1,0 +1,64 @@
+"""Import the UNMODIFIED reference (/root/reference/avion) on CPU.  TEST INFRASTRUCTURE ONLY.
+
+Works only in the build container (the GPU box has no /root/reference).  Two absent packages are shimmed
+(SURVEY.md section 8c): ``timm.models.layers`` (3 symbols; DropPath rates are 0 in every config) and ``clip``
+(only used to download OpenAI weights, avion/models/model_clip.py:150-152).  flash-attn needs CUDA to execute,
+so the reference is built with use_flash_attn=False: same math, nn.MultiheadAttention naming; the bijection to
+the flash naming is avion/models/utils.py:42-49.
+"""
+import os
+import sys
+import types
+
+import torch
+
+REFERENCE_ROOT = "/root/reference"
+
+
+def available() -> bool:
+    return os.path.isdir(os.path.join(REFERENCE_ROOT, "avion"))
+
+
+def import_reference():
+    if not available():
+        raise RuntimeError("reference tree not present (expected only in the build container)")
+    if "timm.models.layers" not in sys.modules:
+        timm, models, layers = (types.ModuleType(n) for n in ("timm", "timm.models", "timm.models.layers"))
+        layers.trunc_normal_ = torch.nn.init.trunc_normal_
+        layers.to_2tuple = lambda x: x if isinstance(x, tuple) else (x, x)
+        layers.DropPath = torch.nn.Identity
+        timm.models, models.layers = models, layers
+        sys.modules.update({"timm": timm, "timm.models": models, "timm.models.layers": layers})
+    sys.modules.setdefault("clip", types.ModuleType("clip"))
+    if REFERENCE_ROOT not in sys.path:
+        sys.path.insert(0, REFERENCE_ROOT)
+    from avion.models.transformer import VisionTransformer, TextTransformer
+    from avion.models.model_clip import CLIP
+    from avion.losses.losses import ClipLoss
+    return VisionTransformer, TextTransformer, CLIP, ClipLoss
+
+
+_FLASH_TO_MHA = {"attn.Wqkv.weight": "attn.in_proj_weight", "attn.Wqkv.bias": "attn.in_proj_bias",
+                 "mlp.fc1.": "mlp.c_fc.", "mlp.fc2.": "mlp.c_proj."}
+
+
+def to_reference_key(k: str) -> str:
+    """flash+fast_conv1 key (our boundary) -> key of the non-flash reference module (utils.py:42-49 inverted)."""
+    if k.startswith("visual.transformer."):
+        for a, b in _FLASH_TO_MHA.items():
+            k = k.replace(a, b)
+    return k
+
+
+def build_reference_clip(cfg, sd):
+    """Reference CLIP built with the factory's literal arguments (model_clip.py:118-148) and loaded with sd."""
+    VisionTransformer, TextTransformer, CLIP, _ = import_reference()
+    vis = VisionTransformer(cfg.image_size, cfg.patch, cfg.width, cfg.layers, cfg.heads, 4,
+                            output_dim=cfg.embed_dim, num_frames=cfg.frames,
+                            use_fast_conv1=True, use_flash_attn=False)
+    txt = TextTransformer(context_length=cfg.ctx, vocab_size=cfg.vocab, width=cfg.t_width, heads=cfg.t_heads,
+                          layers=cfg.t_layers, output_dim=cfg.embed_dim, causal_mask=True)
+    model = CLIP(embed_dim=cfg.embed_dim, vision_model=vis, text_model=txt)
+    missing, unexpected = model.load_state_dict({to_reference_key(k): v for k, v in sd.items()}, strict=True)
+    assert not missing and not unexpected
+    return model.float()
