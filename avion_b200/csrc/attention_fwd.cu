@@ -1,0 +1,267 @@
+// V4 forward: flash-style attention on tcgen05, head dim 64 (non-causal for the video tower, causal for the text tower).
+// Replaces flash_attn_qkvpacked_func (reached from avion/models/transformer.py:148) and the masked
+// nn.MultiheadAttention of the text tower (:140-146,447-453).
+//
+// One CTA per (clip, head, PAIR of 128-row query tiles).  Roles:
+//   warps 0-3 / 4-7 : softmax group 0 / 1 (one query row per thread: S tile read from TMEM, online softmax in fp32
+//                     registers, P written to swizzled smem as bf16, O accumulated in registers)
+//   warp 8          : MMA issuer  (S_w = Q_w K_j^T and O_w = P_w V_j on tcgen05, accumulators in TMEM)
+//   warp 9          : TMA producer (Q tiles once, then a 3-stage K/V ring shared by both groups)
+// The two groups ping-pong: while one does softmax (MUFU/FMA bound at head dim 64) the other's MMAs run.
+#include "common.cuh"
+#include "../../include/avion_b200.h"
+
+namespace {
+using namespace avn;
+
+constexpr int TILE = 128, HD = 64, KV_STAGES = 3;
+constexpr int NTHREADS = 320;
+constexpr int Q_BYTES = TILE * HD * 2;            // 16 KB
+constexpr int KV_BYTES = TILE * HD * 2;           // 16 KB each for K and V
+constexpr int P_BYTES = TILE * TILE * 2;          // 32 KB
+constexpr int OFF_Q = 0;
+constexpr int OFF_K = OFF_Q + 2 * Q_BYTES;
+constexpr int OFF_V = OFF_K + KV_STAGES * KV_BYTES;
+constexpr int OFF_P = OFF_V + KV_STAGES * KV_BYTES;
+constexpr int OFF_BAR = OFF_P + 2 * P_BYTES;
+constexpr int SMEM_TOTAL = OFF_BAR + 256 + 1024;
+constexpr uint32_t TM_S = 0, TM_O = 256;          // TMEM columns: S_w at w*128, O_w at 256 + w*64
+
+struct Bars {
+    uint64_t q_full;
+    uint64_t kv_full[KV_STAGES], kv_empty[KV_STAGES];
+    uint64_t s_full[2], s_free[2], p_ready[2], o_full[2];
+    uint32_t tmem_ptr;
+};
+
+__global__ void __launch_bounds__(NTHREADS, 1)
+attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmO, float* __restrict__ lse,
+                int S, int H, float scale_log2, int causal) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    Bars* bars = (Bars*)(smem + OFF_BAR);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int b = blockIdx.z, h = blockIdx.y;
+    const int q_tiles = (S + TILE - 1) / TILE;
+    const int kv_tiles = q_tiles;
+    const int qt[2] = {(int)blockIdx.x * 2, (int)blockIdx.x * 2 + 1};
+    int nkv[2];
+#pragma unroll
+    for (int w = 0; w < 2; ++w) nkv[w] = qt[w] >= q_tiles ? 0 : (causal ? min(kv_tiles, qt[w] + 1) : kv_tiles);
+    const int nkv_max = max(nkv[0], nkv[1]);
+
+    if (threadIdx.x == 0) {
+        tma_prefetch_desc(&tmQKV);
+        tma_prefetch_desc(&tmO);
+        mbar_init(&bars->q_full, 1);
+        for (int i = 0; i < KV_STAGES; ++i) { mbar_init(&bars->kv_full[i], 1); mbar_init(&bars->kv_empty[i], 1); }
+        for (int w = 0; w < 2; ++w) {
+            mbar_init(&bars->s_full[w], 1); mbar_init(&bars->s_free[w], 128);
+            mbar_init(&bars->p_ready[w], 128); mbar_init(&bars->o_full[w], 1);
+        }
+        fence_barrier_init();
+    }
+    if (warp == 8) tmem_alloc(&bars->tmem_ptr, 512);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = bars->tmem_ptr;
+
+    if (warp == 9) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            const int n_q = (qt[1] < q_tiles) ? 2 : 1;
+            mbar_expect_tx(&bars->q_full, n_q * Q_BYTES);
+            for (int w = 0; w < n_q; ++w) tma_load_3d(smem + OFF_Q + w * Q_BYTES, &tmQKV, &bars->q_full, h * HD, qt[w] * TILE, b);
+            for (int j = 0; j < nkv_max; ++j) {
+                const int st = j % KV_STAGES;
+                mbar_wait(&bars->kv_empty[st], ((j / KV_STAGES) & 1) ^ 1);
+                mbar_expect_tx(&bars->kv_full[st], 2 * KV_BYTES);
+                tma_load_3d(smem + OFF_K + st * KV_BYTES, &tmQKV, &bars->kv_full[st], (H + h) * HD, j * TILE, b);
+                tma_load_3d(smem + OFF_V + st * KV_BYTES, &tmQKV, &bars->kv_full[st], (2 * H + h) * HD, j * TILE, b);
+            }
+        }
+    } else if (warp == 8) {
+        // ===================== MMA issuer =====================
+        if (lane == 0 && nkv_max > 0) {
+            constexpr uint32_t idesc_s = umma_idesc_bf16(TILE, TILE, false, false);
+            constexpr uint32_t idesc_o = umma_idesc_bf16(TILE, HD, false, true);
+            auto issue_s = [&](int w, int j) {
+                if (j > 0) { mbar_wait(&bars->s_free[w], (j - 1) & 1); tc_fence_after(); }
+                const uint32_t qa = smem_u32(smem + OFF_Q + w * Q_BYTES);
+                const uint32_t ka = smem_u32(smem + OFF_K + (j % KV_STAGES) * KV_BYTES);
+#pragma unroll
+                for (int k = 0; k < HD / 16; ++k)
+                    umma_ss(tmem_base + TM_S + w * TILE, umma_smem_desc(qa + k * 32, 16, 1024), umma_smem_desc(ka + k * 32, 16, 1024),
+                            idesc_s, k > 0 ? 1u : 0u);
+                umma_commit(&bars->s_full[w]);
+            };
+            mbar_wait(&bars->q_full, 0);
+            mbar_wait(&bars->kv_full[0], 0);
+            tc_fence_after();
+            for (int w = 0; w < 2; ++w) if (nkv[w] > 0) issue_s(w, 0);
+            for (int j = 0; j < nkv_max; ++j) {
+                const int st = j % KV_STAGES;
+                if (j + 1 < nkv_max) {
+                    mbar_wait(&bars->kv_full[(j + 1) % KV_STAGES], ((j + 1) / KV_STAGES) & 1);
+                    tc_fence_after();
+                    for (int w = 0; w < 2; ++w) if (j + 1 < nkv[w]) issue_s(w, j + 1);
+                }
+                const uint32_t va = smem_u32(smem + OFF_V + st * KV_BYTES);
+                for (int w = 0; w < 2; ++w) {
+                    if (j >= nkv[w]) continue;
+                    mbar_wait(&bars->p_ready[w], j & 1);
+                    tc_fence_after();
+                    const uint32_t pa = smem_u32(smem + OFF_P + w * P_BYTES);
+#pragma unroll
+                    for (int k = 0; k < TILE / 16; ++k)
+                        umma_ss(tmem_base + TM_O + w * HD, umma_smem_desc(pa + (k >> 2) * (P_BYTES / 2) + (k & 3) * 32, 16, 1024),
+                                umma_smem_desc(va + k * 2048, 8192, 1024), idesc_o, k > 0 ? 1u : 0u);
+                    umma_commit(&bars->o_full[w]);
+                }
+                umma_commit(&bars->kv_empty[st]);
+            }
+        }
+    } else {
+        // ===================== softmax groups =====================
+        const int w = warp >> 2;
+        const int row = (warp & 3) * 32 + lane;
+        const int n_my = nkv[w];
+        if (n_my > 0) {
+            const int q0 = qt[w] * TILE;
+            const int qrow = q0 + row;
+            const uint32_t t_s = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + TM_S + w * TILE;
+            const uint32_t t_o = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + TM_O + w * HD;
+            uint8_t* sP = smem + OFF_P + w * P_BYTES;
+            float o[HD];
+#pragma unroll
+            for (int i = 0; i < HD; ++i) o[i] = 0.f;
+            float m = -INFINITY, l = 0.f;
+            for (int j = 0; j < n_my; ++j) {
+                const int kv0 = j * TILE;
+                const bool need_mask = (kv0 + TILE > S) || (causal && kv0 + TILE - 1 > q0);
+                const int limit = causal ? min(S - kv0, qrow - kv0 + 1) : (S - kv0);   // columns [0, limit) are valid
+                mbar_wait(&bars->s_full[w], j & 1);
+                tc_fence_after();
+                // pass 1: row maximum
+                float mx = -INFINITY;
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    uint32_t v[32];
+                    tmem_ld32(t_s + c * 32, v);
+                    tmem_ld_wait();
+                    if (need_mask) {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) if (c * 32 + i < limit) mx = fmaxf(mx, __uint_as_float(v[i]));
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(v[i]));
+                    }
+                }
+                const float m_new = fmaxf(m, mx * scale_log2);
+                const float alpha = exp2f(m - m_new);
+                // pass 2: probabilities -> bf16 -> smem (two K-major 128B-swizzled [128][64] sub-tiles)
+                float rs = 0.f;
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    uint32_t v[32];
+                    tmem_ld32(t_s + c * 32, v);
+                    tmem_ld_wait();
+                    if (c == 3) { tc_fence_before(); mbar_arrive(&bars->s_free[w]); }
+                    float p[32];
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) {
+                        float e = exp2f(fmaf(__uint_as_float(v[i]), scale_log2, -m_new));
+                        if (need_mask && c * 32 + i >= limit) e = 0.f;
+                        p[i] = e;
+                        rs += e;
+                    }
+                    uint8_t* sub = sP + (c >> 1) * (P_BYTES / 2) + row * 128;
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const int c16 = (c & 1) * 4 + i;
+                        *(uint4*)(sub + ((c16 ^ (row & 7)) << 4)) =
+                            make_uint4(pack_bf16(p[8 * i], p[8 * i + 1]), pack_bf16(p[8 * i + 2], p[8 * i + 3]),
+                                       pack_bf16(p[8 * i + 4], p[8 * i + 5]), pack_bf16(p[8 * i + 6], p[8 * i + 7]));
+                    }
+                }
+                l = fmaf(l, alpha, rs);
+                m = m_new;
+                fence_proxy_async_smem();
+                // fold the previous tile's P*V into the register accumulator, then rescale to the new maximum
+                if (j > 0) {
+                    mbar_wait(&bars->o_full[w], (j - 1) & 1);
+                    tc_fence_after();
+#pragma unroll
+                    for (int c = 0; c < 2; ++c) {
+                        uint32_t v[32];
+                        tmem_ld32(t_o + c * 32, v);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) o[c * 32 + i] = (o[c * 32 + i] + __uint_as_float(v[i])) * alpha;
+                    }
+                    tc_fence_before();
+                }
+                mbar_arrive(&bars->p_ready[w]);
+            }
+            // last tile's P*V
+            mbar_wait(&bars->o_full[w], (n_my - 1) & 1);
+            tc_fence_after();
+            const float inv_l = 1.f / l;
+#pragma unroll
+            for (int c = 0; c < 2; ++c) {
+                uint32_t v[32];
+                tmem_ld32(t_o + c * 32, v);
+                tmem_ld_wait();
+#pragma unroll
+                for (int i = 0; i < 32; ++i) o[c * 32 + i] = (o[c * 32 + i] + __uint_as_float(v[i])) * inv_l;
+            }
+            if (qrow < S) lse[((long long)b * H + h) * S + qrow] = (m + log2f(l)) * 0.6931471805599453f;
+            // O tile -> swizzled smem (reuses this group's P buffer: its last MMA has completed) -> TMA store
+            uint8_t* stg = sP + row * 128;
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+                *(uint4*)(stg + ((i ^ (row & 7)) << 4)) =
+                    make_uint4(pack_bf16(o[8 * i], o[8 * i + 1]), pack_bf16(o[8 * i + 2], o[8 * i + 3]),
+                               pack_bf16(o[8 * i + 4], o[8 * i + 5]), pack_bf16(o[8 * i + 6], o[8 * i + 7]));
+            fence_proxy_async_smem();
+            named_bar_sync(1 + w, 128);
+            if ((threadIdx.x & 127) == 0) {
+                tma_store_3d(&tmO, sP, h * HD, q0, b);
+                tma_commit_group();
+                tma_wait_group0();
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 8) tmem_dealloc(tmem_base, 512);
+}
+}  // namespace
+
+extern "C" int avn_attn_fwd(const void* qkv, void* out, float* lse, int B, int S, int H, float scale, int causal, avn_stream_t stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    AVN_REQUIRE(qkv && out && lse, "attn_fwd: null pointer");
+    AVN_REQUIRE(B > 0 && S > 0 && H > 0, "attn_fwd: bad sizes B=%d S=%d H=%d", B, S, H);
+    AVN_REQUIRE(((uintptr_t)qkv % 16) == 0 && ((uintptr_t)out % 16) == 0, "attn_fwd: pointers must be 16-byte aligned");
+    CUtensorMap tmQKV, tmO;
+    int rc;
+    {
+        uint64_t dims[3] = {(uint64_t)3 * H * HD, (uint64_t)S, (uint64_t)B};
+        uint64_t str[2] = {(uint64_t)3 * H * HD * 2, (uint64_t)S * 3 * H * HD * 2};
+        uint32_t box[3] = {HD, TILE, 1};
+        if ((rc = avn_make_tmap(&tmQKV, qkv, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, 3, dims, str, box, true))) return rc;
+    }
+    {
+        uint64_t dims[3] = {(uint64_t)H * HD, (uint64_t)S, (uint64_t)B};
+        uint64_t str[2] = {(uint64_t)H * HD * 2, (uint64_t)S * H * HD * 2};
+        uint32_t box[3] = {HD, TILE, 1};
+        if ((rc = avn_make_tmap(&tmO, out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, 3, dims, str, box, true))) return rc;
+    }
+    const int q_tiles = (S + TILE - 1) / TILE;
+    AVN_CHECK_CUDA(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_TOTAL));
+    dim3 grid((q_tiles + 1) / 2, H, B);
+    attn_fwd_kernel<<<grid, NTHREADS, SMEM_TOTAL, stream>>>(tmQKV, tmO, lse, S, H, scale * 1.4426950408889634f, causal);
+    AVN_CHECK_CUDA(cudaGetLastError());
+    return AVN_OK;
+}

@@ -1,0 +1,379 @@
+// bf16 GEMM for sm_100a: persistent, warp-specialised.
+//   warp 0      : TMA producer   (cp.async.bulk.tensor -> 4-stage smem ring, 128B swizzle)
+//   warp 1      : MMA issuer     (one lane issues tcgen05.mma, fp32 accumulators in TMEM, double-buffered)
+//   warps 2..9  : epilogue       (tcgen05.ld -> bias / GELU(erf) / residual / dGELU -> swizzled smem -> TMA store,
+//                                 or fp32 TMA reduce-add for split-K weight gradients)
+// Tile 128 x BN x 64 (BN = 128 or 256).  Operand majors:
+//   NT: A K-major, B K-major        (forward:  X[M,K] * W[N,K]^T)
+//   NN: A K-major, B MN-major       (dgrad:    dY[M,N'] * W[N',K'])
+//   TN: A MN-major, B MN-major      (wgrad:    dY[tok,N]^T * X[tok,K], contraction over tokens, split-K)
+// Replaces the cuBLAS calls behind nn.Linear / FlashMHA / FlashMlp in avion/models/transformer.py:116-120,135,227,320.
+#include "common.cuh"
+#include "../../include/avion_b200.h"
+
+namespace {
+using namespace avn;
+
+constexpr int BM = 128, BK = 64, STAGES = 4;
+constexpr int EPI_WARPS = 8;
+constexpr int NTHREADS = 64 + EPI_WARPS * 32;
+constexpr int A_STAGE_BYTES = BM * BK * 2;       // 16 KB
+constexpr int STG_BYTES = 128 * 128;             // one 128-row x 128-byte staging tile per epilogue group
+
+struct KParams {
+    int M, N, K, batch;
+    int m_tiles, n_tiles, splits, kblocks, kb_per_split, total_kb;
+    const float* bias;
+    const __nv_bfloat16* R;
+    long long ldr, r_batch_stride;
+};
+
+template <int BN>
+struct Smem {
+    static constexpr int B_STAGE_BYTES = BN * BK * 2;
+    static constexpr int OFF_A = 0;
+    static constexpr int OFF_B = OFF_A + STAGES * A_STAGE_BYTES;
+    static constexpr int OFF_STG = OFF_B + STAGES * B_STAGE_BYTES;
+    static constexpr int OFF_BIAS = OFF_STG + 2 * STG_BYTES;
+    static constexpr int OFF_BAR = OFF_BIAS + BN * 4;
+    static constexpr int TOTAL = OFF_BAR + 256 + 1024;   // + alignment slack
+};
+
+template <int BN, int MODE, int EPI>
+__global__ void __launch_bounds__(NTHREADS, 1)
+gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+            const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmC2, const KParams p) {
+    constexpr bool A_MN = (MODE == AVN_GEMM_TN);
+    constexpr bool B_MN = (MODE != AVN_GEMM_NT);
+    using L = Smem<BN>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    uint8_t* sA = smem + L::OFF_A;
+    uint8_t* sB = smem + L::OFF_B;
+    uint8_t* sStg = smem + L::OFF_STG;
+    float* sBias = (float*)(smem + L::OFF_BIAS);
+    uint64_t* full_bar = (uint64_t*)(smem + L::OFF_BAR);
+    uint64_t* empty_bar = full_bar + STAGES;
+    uint64_t* tfull_bar = empty_bar + STAGES;
+    uint64_t* tempty_bar = tfull_bar + 2;
+    uint32_t* tmem_ptr = (uint32_t*)(tempty_bar + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmA);
+        tma_prefetch_desc(&tmB);
+        tma_prefetch_desc(&tmC);
+        for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], EPI_WARPS); }
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_ptr, 2 * BN);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr;
+
+    const int total_tiles = (MODE == AVN_GEMM_TN ? p.splits : p.batch) * p.m_tiles * p.n_tiles;
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            int stage = 0; uint32_t phase = 0;
+            for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+                int n_blk = t % p.n_tiles; int r = t / p.n_tiles;
+                int m_blk = r % p.m_tiles; int outer = r / p.m_tiles;       // batch (NT/NN) or split (TN)
+                int kb0 = 0, kb1 = p.kblocks;
+                if (MODE == AVN_GEMM_TN) { kb0 = outer * p.kb_per_split; kb1 = min(p.total_kb, kb0 + p.kb_per_split); }
+                const int m0 = m_blk * BM, n0 = n_blk * BN;
+                for (int kb = kb0; kb < kb1; ++kb) {
+                    mbar_wait(&empty_bar[stage], phase ^ 1);
+                    uint8_t* a = sA + stage * A_STAGE_BYTES;
+                    uint8_t* b = sB + stage * L::B_STAGE_BYTES;
+                    mbar_expect_tx(&full_bar[stage], A_STAGE_BYTES + L::B_STAGE_BYTES);
+                    if (MODE == AVN_GEMM_TN) {
+                        int kbatch = kb / p.kblocks, krow = (kb % p.kblocks) * BK;
+#pragma unroll
+                        for (int j = 0; j < BM / 64; ++j) tma_load_3d(a + j * 8192, &tmA, &full_bar[stage], m0 + 64 * j, krow, kbatch);
+#pragma unroll
+                        for (int j = 0; j < BN / 64; ++j) tma_load_3d(b + j * 8192, &tmB, &full_bar[stage], n0 + 64 * j, krow, kbatch);
+                    } else {
+                        tma_load_3d(a, &tmA, &full_bar[stage], kb * BK, m0, outer);
+                        if (MODE == AVN_GEMM_NT) {
+                            tma_load_3d(b, &tmB, &full_bar[stage], kb * BK, n0, 0);
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < BN / 64; ++j) tma_load_3d(b + j * 8192, &tmB, &full_bar[stage], n0 + 64 * j, kb * BK, 0);
+                        }
+                    }
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        constexpr uint32_t idesc = umma_idesc_bf16(BM, BN, A_MN, B_MN);
+        constexpr uint32_t a_lbo = A_MN ? 8192 : 16, b_lbo = B_MN ? 8192 : 16;
+        constexpr uint32_t a_adv = A_MN ? 2048 : 32, b_adv = B_MN ? 2048 : 32;    // bytes per UMMA_K = 16
+        int stage = 0; uint32_t phase = 0;
+        int acc = 0; uint32_t acc_phase = 0;
+        for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+            int outer = (t / p.n_tiles) / p.m_tiles;
+            int kb0 = 0, kb1 = p.kblocks;
+            if (MODE == AVN_GEMM_TN) { kb0 = outer * p.kb_per_split; kb1 = min(p.total_kb, kb0 + p.kb_per_split); }
+            mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+            tc_fence_after();
+            const uint32_t d_tmem = tmem_base + acc * BN;
+            for (int kb = kb0; kb < kb1; ++kb) {
+                mbar_wait(&full_bar[stage], phase);
+                tc_fence_after();
+                if (lane == 0) {
+                    const uint32_t a_addr = smem_u32(sA + stage * A_STAGE_BYTES);
+                    const uint32_t b_addr = smem_u32(sB + stage * L::B_STAGE_BYTES);
+#pragma unroll
+                    for (int k = 0; k < BK / 16; ++k) {
+                        uint64_t ad = umma_smem_desc(a_addr + k * a_adv, a_lbo, 1024);
+                        uint64_t bd = umma_smem_desc(b_addr + k * b_adv, b_lbo, 1024);
+                        umma_ss(d_tmem, ad, bd, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+                    }
+                    umma_commit(&empty_bar[stage]);
+                    if (kb == kb1 - 1) umma_commit(&tfull_bar[acc]);
+                }
+                __syncwarp();
+                if (++stage == STAGES) { stage = 0; phase ^= 1; }
+            }
+            if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        }
+    } else {
+        // ===================== epilogue =====================
+        const int ew = warp - 2;
+        const int g = ew >> 2;                  // column half handled by this group of 4 warps
+        const int q = warp & 3;                 // TMEM lane quarter this warp may access
+        const int row = q * 32 + lane;          // row inside the tile
+        const int gtid = (ew & 3) * 32 + lane;  // thread index inside the group
+        const int bar_id = 1 + g;
+        uint8_t* stg = sStg + g * STG_BYTES;
+        float* bias_s = sBias + g * (BN / 2);
+        constexpr int UNITS = BN / 2 / 32;      // 32-column units per group
+        int acc = 0; uint32_t acc_phase = 0;
+        for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+            int n_blk = t % p.n_tiles; int r = t / p.n_tiles;
+            int m_blk = r % p.m_tiles; int outer = r / p.m_tiles;
+            const int mb = (MODE == AVN_GEMM_TN) ? 0 : outer;
+            const int m0 = m_blk * BM, n0 = n_blk * BN + g * (BN / 2);
+            const int m = m0 + row;
+            if (EPI == AVN_EPI_BIAS || EPI == AVN_EPI_BIAS_GELU || EPI == AVN_EPI_BIAS_GELU_DUAL || EPI == AVN_EPI_BIAS_RESIDUAL) {
+                named_bar_sync(bar_id, 128);    // previous tile's readers of bias_s are done
+                if (gtid < BN / 2) bias_s[gtid] = (p.bias != nullptr && n0 + gtid < p.N) ? p.bias[n0 + gtid] : 0.f;
+                named_bar_sync(bar_id, 128);
+            }
+            mbar_wait(&tfull_bar[acc], acc_phase);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN + g * (BN / 2);
+            uint32_t keep[(EPI == AVN_EPI_BIAS_GELU_DUAL) ? 32 : 1];
+#pragma unroll
+            for (int u = 0; u < UNITS; ++u) {
+                uint32_t v[32];
+                tmem_ld32(taddr + u * 32, v);
+                tmem_ld_wait();
+                if (u == UNITS - 1) {           // accumulator fully read: hand the TMEM buffer back to the MMA warp
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+                }
+                const int nc = n0 + u * 32;     // first global column of this unit
+                if (EPI == AVN_EPI_F32_ADD) {
+                    if (gtid == 0) tma_wait_group_read0();
+                    named_bar_sync(bar_id, 128);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        uint4 w = make_uint4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+                        *(uint4*)(stg + row * 128 + ((i ^ (row & 7)) << 4)) = w;
+                    }
+                    fence_proxy_async_smem();
+                    named_bar_sync(bar_id, 128);
+                    if (gtid == 0) { tma_reduce_add_3d(&tmC, stg, nc, m0, mb); tma_commit_group(); }
+                } else {
+                    float f[32];
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+                    if (EPI == AVN_EPI_BIAS || EPI == AVN_EPI_BIAS_GELU || EPI == AVN_EPI_BIAS_GELU_DUAL || EPI == AVN_EPI_BIAS_RESIDUAL) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) f[j] += bias_s[u * 32 + j];
+                    }
+                    if (EPI == AVN_EPI_BIAS_RESIDUAL || EPI == AVN_EPI_DGELU) {
+                        const __nv_bfloat16* rp = p.R + (long long)mb * p.r_batch_stride + (long long)m * p.ldr + nc;
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            uint4 rv = make_uint4(0, 0, 0, 0);
+                            if (m < p.M && nc + 8 * i + 8 <= p.N) rv = __ldg((const uint4*)(rp + 8 * i));
+                            const uint32_t rr[4] = {rv.x, rv.y, rv.z, rv.w};
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) {
+                                float2 x = unpack_bf16(rr[e]);
+                                if (EPI == AVN_EPI_BIAS_RESIDUAL) { f[8 * i + 2 * e] += x.x; f[8 * i + 2 * e + 1] += x.y; }
+                                else { f[8 * i + 2 * e] *= gelu_erf_grad(x.x); f[8 * i + 2 * e + 1] *= gelu_erf_grad(x.y); }
+                            }
+                        }
+                    }
+                    if (EPI == AVN_EPI_BIAS_GELU_DUAL) {
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) keep[(u & 1) * 16 + j] = pack_bf16(f[2 * j], f[2 * j + 1]);
+                    }
+                    if (EPI == AVN_EPI_BIAS_GELU || EPI == AVN_EPI_BIAS_GELU_DUAL) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) f[j] = gelu_erf(f[j]);
+                    }
+                    if ((u & 1) == 0) {         // starting a new 64-column staging tile
+                        if (gtid == 0) tma_wait_group_read0();
+                        named_bar_sync(bar_id, 128);
+                    }
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        uint4 w = make_uint4(pack_bf16(f[8 * i], f[8 * i + 1]), pack_bf16(f[8 * i + 2], f[8 * i + 3]),
+                                             pack_bf16(f[8 * i + 4], f[8 * i + 5]), pack_bf16(f[8 * i + 6], f[8 * i + 7]));
+                        const int c16 = (u & 1) * 4 + i;
+                        *(uint4*)(stg + row * 128 + ((c16 ^ (row & 7)) << 4)) = w;
+                    }
+                    if ((u & 1) == 1) {
+                        fence_proxy_async_smem();
+                        named_bar_sync(bar_id, 128);
+                        if (gtid == 0) { tma_store_3d(&tmC, stg, nc - 32, m0, mb); tma_commit_group(); }
+                        if (EPI == AVN_EPI_BIAS_GELU_DUAL) {
+                            if (gtid == 0) tma_wait_group_read0();
+                            named_bar_sync(bar_id, 128);
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) {
+                                uint4 w = make_uint4(keep[4 * i], keep[4 * i + 1], keep[4 * i + 2], keep[4 * i + 3]);
+                                *(uint4*)(stg + row * 128 + ((i ^ (row & 7)) << 4)) = w;
+                            }
+                            fence_proxy_async_smem();
+                            named_bar_sync(bar_id, 128);
+                            if (gtid == 0) { tma_store_3d(&tmC2, stg, nc - 32, m0, mb); tma_commit_group(); }
+                        }
+                    }
+                }
+            }
+            if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        }
+        if (gtid == 0) tma_wait_group0();
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem_base, 2 * BN);
+}
+
+template <int BN, int MODE, int EPI>
+int launch(const avn_gemm_desc* d, cudaStream_t stream) {
+    using L = Smem<BN>;
+    CUtensorMap tmA, tmB, tmC, tmC2;
+    const bool tn = (MODE == AVN_GEMM_TN);
+    int rc;
+    // ---- A
+    if (!tn) {
+        uint64_t dims[3] = {(uint64_t)d->K, (uint64_t)d->M, (uint64_t)d->batch};
+        uint64_t str[2] = {(uint64_t)d->lda * 2, (uint64_t)(d->batch > 1 ? d->a_batch_stride : d->lda * (int64_t)d->M) * 2};
+        uint32_t box[3] = {64, 128, 1};
+        if ((rc = avn_make_tmap(&tmA, d->A, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, 3, dims, str, box, true))) return rc;
+    } else {
+        uint64_t dims[3] = {(uint64_t)d->M, (uint64_t)d->K, (uint64_t)d->batch};
+        uint64_t str[2] = {(uint64_t)d->lda * 2, (uint64_t)(d->batch > 1 ? d->a_batch_stride : d->lda * (int64_t)d->K) * 2};
+        uint32_t box[3] = {64, 64, 1};
+        if ((rc = avn_make_tmap(&tmA, d->A, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, 3, dims, str, box, true))) return rc;
+    }
+    // ---- B
+    if (MODE == AVN_GEMM_NT) {
+        uint64_t dims[3] = {(uint64_t)d->K, (uint64_t)d->N, 1};
+        uint64_t str[2] = {(uint64_t)d->ldb * 2, (uint64_t)d->ldb * 2 * (uint64_t)d->N};
+        uint32_t box[3] = {64, (uint32_t)BN, 1};
+        if ((rc = avn_make_tmap(&tmB, d->B, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, 3, dims, str, box, true))) return rc;
+    } else {
+        const int bb = tn ? d->batch : 1;
+        uint64_t dims[3] = {(uint64_t)d->N, (uint64_t)d->K, (uint64_t)bb};
+        uint64_t str[2] = {(uint64_t)d->ldb * 2, (uint64_t)(bb > 1 ? d->b_batch_stride : d->ldb * (int64_t)d->K) * 2};
+        uint32_t box[3] = {64, 64, 1};
+        if ((rc = avn_make_tmap(&tmB, d->B, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, 3, dims, str, box, true))) return rc;
+    }
+    // ---- C (and C2)
+    const int cb = tn ? 1 : d->batch;
+    if (EPI == AVN_EPI_F32_ADD) {
+        uint64_t dims[3] = {(uint64_t)d->N, (uint64_t)d->M, 1};
+        uint64_t str[2] = {(uint64_t)d->ldc * 4, (uint64_t)d->ldc * 4 * (uint64_t)d->M};
+        uint32_t box[3] = {32, 128, 1};
+        if ((rc = avn_make_tmap(&tmC, d->C, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, 3, dims, str, box, true))) return rc;
+        tmC2 = tmC;
+    } else {
+        uint64_t dims[3] = {(uint64_t)d->N, (uint64_t)d->M, (uint64_t)cb};
+        uint64_t str[2] = {(uint64_t)d->ldc * 2, (uint64_t)(cb > 1 ? d->c_batch_stride : d->ldc * (int64_t)d->M) * 2};
+        uint32_t box[3] = {64, 128, 1};
+        if ((rc = avn_make_tmap(&tmC, d->C, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, 3, dims, str, box, true))) return rc;
+        tmC2 = tmC;
+        if (EPI == AVN_EPI_BIAS_GELU_DUAL)
+            if ((rc = avn_make_tmap(&tmC2, d->C2, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, 3, dims, str, box, true))) return rc;
+    }
+    KParams p;
+    p.M = d->M; p.N = d->N; p.K = d->K; p.batch = d->batch;
+    p.m_tiles = (d->M + BM - 1) / BM;
+    p.n_tiles = (d->N + BN - 1) / BN;
+    p.kblocks = (d->K + BK - 1) / BK;
+    p.total_kb = p.kblocks * d->batch;
+    int splits = tn ? (d->splits > 0 ? d->splits : 1) : 1;
+    if (splits > p.total_kb) splits = p.total_kb;
+    p.kb_per_split = (p.total_kb + splits - 1) / splits;
+    p.splits = (p.total_kb + p.kb_per_split - 1) / p.kb_per_split;
+    p.bias = d->bias;
+    p.R = (const __nv_bfloat16*)d->R; p.ldr = d->ldr; p.r_batch_stride = d->r_batch_stride;
+    const int total_tiles = (tn ? p.splits : d->batch) * p.m_tiles * p.n_tiles;
+    int grid = avn_num_sms();
+    if (grid > total_tiles) grid = total_tiles;
+    auto kern = gemm_kernel<BN, MODE, EPI>;
+    AVN_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
+    kern<<<grid, NTHREADS, L::TOTAL, stream>>>(tmA, tmB, tmC, tmC2, p);
+    AVN_CHECK_CUDA(cudaGetLastError());
+    return AVN_OK;
+}
+
+template <int MODE, int EPI>
+int launch_bn(const avn_gemm_desc* d, cudaStream_t stream) {
+    // 256-wide tiles when N fills them and there are enough tiles to occupy the SMs; else 128-wide.
+    const long long tiles256 = (long long)((d->M + 127) / 128) * ((d->N + 255) / 256) * (MODE == AVN_GEMM_TN ? 1 : d->batch);
+    if (d->N % 256 == 0 && (tiles256 >= 2 * avn_num_sms() || MODE == AVN_GEMM_TN)) return launch<256, MODE, EPI>(d, stream);
+    return launch<128, MODE, EPI>(d, stream);
+}
+}  // namespace
+
+extern "C" int avn_gemm_bf16(const avn_gemm_desc* d, avn_stream_t stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    AVN_REQUIRE(d != nullptr, "gemm: null descriptor");
+    AVN_REQUIRE(d->M > 0 && d->N > 0 && d->K > 0 && d->batch > 0, "gemm: bad sizes M=%d N=%d K=%d batch=%d", d->M, d->N, d->K, d->batch);
+    AVN_REQUIRE(d->A && d->B && d->C, "gemm: null operand");
+    AVN_REQUIRE(d->lda % 8 == 0 && d->ldb % 8 == 0, "gemm: lda/ldb must be multiples of 8 elements (16 B)");
+    AVN_REQUIRE(((uintptr_t)d->A % 16) == 0 && ((uintptr_t)d->B % 16) == 0 && ((uintptr_t)d->C % 16) == 0, "gemm: operands must be 16-byte aligned");
+    AVN_REQUIRE(d->N % 8 == 0, "gemm: N must be a multiple of 8");
+    const int e = d->epi;
+    if (d->mode == AVN_GEMM_NT) {
+        AVN_REQUIRE(d->ldc % 8 == 0, "gemm: ldc must be a multiple of 8");
+        if (e == AVN_EPI_BIAS_RESIDUAL) AVN_REQUIRE(d->R != nullptr, "gemm: residual epilogue needs R");
+        if (e == AVN_EPI_BIAS_GELU_DUAL) AVN_REQUIRE(d->C2 != nullptr, "gemm: dual epilogue needs C2");
+        switch (e) {
+            case AVN_EPI_NONE: return launch_bn<AVN_GEMM_NT, AVN_EPI_NONE>(d, stream);
+            case AVN_EPI_BIAS: return launch_bn<AVN_GEMM_NT, AVN_EPI_BIAS>(d, stream);
+            case AVN_EPI_BIAS_GELU: return launch_bn<AVN_GEMM_NT, AVN_EPI_BIAS_GELU>(d, stream);
+            case AVN_EPI_BIAS_GELU_DUAL: return launch_bn<AVN_GEMM_NT, AVN_EPI_BIAS_GELU_DUAL>(d, stream);
+            case AVN_EPI_BIAS_RESIDUAL: return launch_bn<AVN_GEMM_NT, AVN_EPI_BIAS_RESIDUAL>(d, stream);
+        }
+    } else if (d->mode == AVN_GEMM_NN) {
+        AVN_REQUIRE(d->ldc % 8 == 0, "gemm: ldc must be a multiple of 8");
+        if (e == AVN_EPI_DGELU) AVN_REQUIRE(d->R != nullptr, "gemm: dgelu epilogue needs R (pre-activation)");
+        switch (e) {
+            case AVN_EPI_NONE: return launch_bn<AVN_GEMM_NN, AVN_EPI_NONE>(d, stream);
+            case AVN_EPI_DGELU: return launch_bn<AVN_GEMM_NN, AVN_EPI_DGELU>(d, stream);
+        }
+    } else if (d->mode == AVN_GEMM_TN) {
+        AVN_REQUIRE(d->ldc % 4 == 0, "gemm: fp32 ldc must be a multiple of 4");
+        AVN_REQUIRE(d->M % 8 == 0, "gemm: TN needs M %% 8 == 0");
+        if (e == AVN_EPI_F32_ADD) return launch_bn<AVN_GEMM_TN, AVN_EPI_F32_ADD>(d, stream);
+    }
+    avn_set_error("gemm: unsupported mode/epilogue combination mode=%d epi=%d", d->mode, e);
+    return AVN_ERR_ARG;
+}

@@ -1,0 +1,200 @@
+// V3: LayerNorm forward / backward over bf16 rows with fp32 statistics (HBM-bound: 4 B/element fwd, 6-8 B/element bwd).
+// Replaces the ATen layer_norm behind ln_pre / ln_1 / ln_2 / ln_post / ln_final
+// (avion/models/transformer.py:35-41,110,124,213,245,264).  One warp per row, 16-byte loads, row kept in registers.
+// The backward also folds in the residual-stream add (x + f(x), transformer.py:148-149) and the column sum that is the
+// bias gradient of the Linear feeding this residual stream.
+#include "common.cuh"
+#include "../../include/avion_b200.h"
+
+namespace {
+using namespace avn;
+
+template <int VPL>   // 16-byte vectors (8 bf16) per lane; D <= VPL*256
+__global__ void __launch_bounds__(256)
+ln_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ beta,
+              __nv_bfloat16* __restrict__ y, float* __restrict__ mean_out, float* __restrict__ rstd_out, long long rows, int D, float eps) {
+    const int lane = threadIdx.x & 31;
+    const long long row = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (row >= rows) return;
+    const int nvec = D >> 3;
+    const uint4* xr = (const uint4*)(x + row * D);
+    float v[VPL][8];
+    float s = 0.f;
+#pragma unroll
+    for (int j = 0; j < VPL; ++j) {
+        const int i = lane + 32 * j;
+        if (i < nvec) {
+            uint4 u = __ldg(xr + i);
+            const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) { float2 f = unpack_bf16(w[e]); v[j][2 * e] = f.x; v[j][2 * e + 1] = f.y; s += f.x + f.y; }
+        } else {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) v[j][e] = 0.f;
+        }
+    }
+    const float mean = warp_sum(s) / D;
+    float q = 0.f;
+#pragma unroll
+    for (int j = 0; j < VPL; ++j)
+        if (lane + 32 * j < nvec) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) { float d = v[j][e] - mean; q += d * d; }
+        }
+    const float rstd = rsqrtf(warp_sum(q) / D + eps);
+    if (lane == 0) {
+        if (mean_out) mean_out[row] = mean;
+        if (rstd_out) rstd_out[row] = rstd;
+    }
+    uint4* yr = (uint4*)(y + row * D);
+#pragma unroll
+    for (int j = 0; j < VPL; ++j) {
+        const int i = lane + 32 * j;
+        if (i < nvec) {
+            const float4 g0 = __ldg((const float4*)(gamma + i * 8)), g1 = __ldg((const float4*)(gamma + i * 8 + 4));
+            const float4 b0 = __ldg((const float4*)(beta + i * 8)), b1 = __ldg((const float4*)(beta + i * 8 + 4));
+            const float g[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+            const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+            float o[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) o[e] = fmaf((v[j][e] - mean) * rstd, g[e], bb[e]);
+            yr[i] = make_uint4(pack_bf16(o[0], o[1]), pack_bf16(o[2], o[3]), pack_bf16(o[4], o[5]), pack_bf16(o[6], o[7]));
+        }
+    }
+}
+
+template <int VPL>
+__global__ void __launch_bounds__(256)
+ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma,
+              const float* __restrict__ mean_in, const float* __restrict__ rstd_in, const __nv_bfloat16* __restrict__ dres,
+              __nv_bfloat16* __restrict__ dx, float* __restrict__ dgamma, float* __restrict__ dbeta, float* __restrict__ dcolsum,
+              long long rows, int D) {
+    extern __shared__ float red[];       // [8 warps][3][VPL*256]
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int nvec = D >> 3;
+    float ag[VPL][8], ab[VPL][8], ac[VPL][8], g[VPL][8];
+#pragma unroll
+    for (int j = 0; j < VPL; ++j) {
+        const int i = lane + 32 * j;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) { ag[j][e] = ab[j][e] = ac[j][e] = 0.f; g[j][e] = (i < nvec) ? __ldg(gamma + i * 8 + e) : 0.f; }
+    }
+    for (long long row = (long long)blockIdx.x * 8 + warp; row < rows; row += (long long)gridDim.x * 8) {
+        const float mean = mean_in[row], rstd = rstd_in[row];
+        const uint4* xr = (const uint4*)(x + row * D);
+        const uint4* dyr = (const uint4*)(dy + row * D);
+        float xh[VPL][8], gy[VPL][8];
+        float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+        for (int j = 0; j < VPL; ++j) {
+            const int i = lane + 32 * j;
+            if (i < nvec) {
+                const uint4 ux = __ldg(xr + i), ud = __ldg(dyr + i);
+                const uint32_t wx[4] = {ux.x, ux.y, ux.z, ux.w}, wd[4] = {ud.x, ud.y, ud.z, ud.w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const float2 fx = unpack_bf16(wx[e]), fd = unpack_bf16(wd[e]);
+                    const float h0 = (fx.x - mean) * rstd, h1 = (fx.y - mean) * rstd;
+                    xh[j][2 * e] = h0; xh[j][2 * e + 1] = h1;
+                    ag[j][2 * e] += fd.x * h0; ag[j][2 * e + 1] += fd.y * h1;
+                    ab[j][2 * e] += fd.x; ab[j][2 * e + 1] += fd.y;
+                    const float t0 = fd.x * g[j][2 * e], t1 = fd.y * g[j][2 * e + 1];
+                    gy[j][2 * e] = t0; gy[j][2 * e + 1] = t1;
+                    s1 += t0 + t1; s2 += t0 * h0 + t1 * h1;
+                }
+            } else {
+#pragma unroll
+                for (int e = 0; e < 8; ++e) { xh[j][e] = 0.f; gy[j][e] = 0.f; }
+            }
+        }
+        const float c1 = warp_sum(s1) / D, c2 = warp_sum(s2) / D;
+        uint4* dxr = (uint4*)(dx + row * D);
+        const uint4* drr = dres ? (const uint4*)(dres + row * D) : nullptr;
+#pragma unroll
+        for (int j = 0; j < VPL; ++j) {
+            const int i = lane + 32 * j;
+            if (i < nvec) {
+                float o[8];
+#pragma unroll
+                for (int e = 0; e < 8; ++e) o[e] = rstd * (gy[j][e] - c1 - xh[j][e] * c2);
+                if (drr) {
+                    const uint4 ur = __ldg(drr + i);
+                    const uint32_t wr[4] = {ur.x, ur.y, ur.z, ur.w};
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) { const float2 f = unpack_bf16(wr[e]); o[2 * e] += f.x; o[2 * e + 1] += f.y; }
+                }
+                const uint4 packed = make_uint4(pack_bf16(o[0], o[1]), pack_bf16(o[2], o[3]), pack_bf16(o[4], o[5]), pack_bf16(o[6], o[7]));
+                dxr[i] = packed;
+                if (dcolsum) {       // column sum of the values actually stored (bf16-rounded), as the next consumer sees them
+                    const uint32_t wp[4] = {packed.x, packed.y, packed.z, packed.w};
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) { const float2 f = unpack_bf16(wp[e]); ac[j][2 * e] += f.x; ac[j][2 * e + 1] += f.y; }
+                }
+            }
+        }
+    }
+    // block reduction of the three column accumulators, then one atomic per column per block
+    const int W = VPL * 256;
+#pragma unroll
+    for (int j = 0; j < VPL; ++j)
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            const int c = (lane + 32 * j) * 8 + e;
+            red[(warp * 3 + 0) * W + c] = ag[j][e];
+            red[(warp * 3 + 1) * W + c] = ab[j][e];
+            red[(warp * 3 + 2) * W + c] = ac[j][e];
+        }
+    __syncthreads();
+    for (int c = threadIdx.x; c < D; c += blockDim.x) {
+        float a = 0.f, b = 0.f, cc = 0.f;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) { a += red[(w * 3 + 0) * W + c]; b += red[(w * 3 + 1) * W + c]; cc += red[(w * 3 + 2) * W + c]; }
+        if (dgamma) atomicAdd(dgamma + c, a);
+        if (dbeta) atomicAdd(dbeta + c, b);
+        if (dcolsum) atomicAdd(dcolsum + c, cc);
+    }
+}
+
+template <int VPL>
+int launch_bwd(const void* dy, const void* x, const float* gamma, const float* mean, const float* rstd, const void* dres, void* dx,
+               float* dgamma, float* dbeta, float* dcolsum, int64_t rows, int D, cudaStream_t stream) {
+    const size_t smem = (size_t)8 * 3 * VPL * 256 * sizeof(float);
+    auto kern = ln_bwd_kernel<VPL>;
+    AVN_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    long long blocks = (rows + 7) / 8;
+    const long long cap = (long long)avn_num_sms() * 4;
+    if (blocks > cap) blocks = cap;
+    kern<<<(int)blocks, 256, smem, stream>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, gamma, mean, rstd,
+                                             (const __nv_bfloat16*)dres, (__nv_bfloat16*)dx, dgamma, dbeta, dcolsum, rows, D);
+    AVN_CHECK_CUDA(cudaGetLastError());
+    return AVN_OK;
+}
+}  // namespace
+
+extern "C" int avn_layernorm_fwd(const void* x, const float* gamma, const float* beta, void* y, float* mean, float* rstd,
+                                 int64_t rows, int D, float eps, avn_stream_t stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    AVN_REQUIRE(x && gamma && beta && y, "layernorm_fwd: null pointer");
+    AVN_REQUIRE(rows > 0 && D > 0 && D % 8 == 0 && D <= 1024, "layernorm_fwd: D=%d must be a multiple of 8 and <= 1024", D);
+    const int blocks = (int)((rows + 7) / 8);
+    const __nv_bfloat16* xp = (const __nv_bfloat16*)x;
+    __nv_bfloat16* yp = (__nv_bfloat16*)y;
+    if (D <= 256) ln_fwd_kernel<1><<<blocks, 256, 0, stream>>>(xp, gamma, beta, yp, mean, rstd, rows, D, eps);
+    else if (D <= 512) ln_fwd_kernel<2><<<blocks, 256, 0, stream>>>(xp, gamma, beta, yp, mean, rstd, rows, D, eps);
+    else if (D <= 768) ln_fwd_kernel<3><<<blocks, 256, 0, stream>>>(xp, gamma, beta, yp, mean, rstd, rows, D, eps);
+    else ln_fwd_kernel<4><<<blocks, 256, 0, stream>>>(xp, gamma, beta, yp, mean, rstd, rows, D, eps);
+    AVN_CHECK_CUDA(cudaGetLastError());
+    return AVN_OK;
+}
+
+extern "C" int avn_layernorm_bwd(const void* dy, const void* x, const float* gamma, const float* mean, const float* rstd,
+                                 const void* dres, void* dx, float* dgamma, float* dbeta, float* dcolsum, int64_t rows, int D,
+                                 avn_stream_t stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    AVN_REQUIRE(dy && x && gamma && mean && rstd && dx, "layernorm_bwd: null pointer");
+    AVN_REQUIRE(rows > 0 && D > 0 && D % 8 == 0 && D <= 1024, "layernorm_bwd: D=%d must be a multiple of 8 and <= 1024", D);
+    if (D <= 256) return launch_bwd<1>(dy, x, gamma, mean, rstd, dres, dx, dgamma, dbeta, dcolsum, rows, D, stream);
+    if (D <= 512) return launch_bwd<2>(dy, x, gamma, mean, rstd, dres, dx, dgamma, dbeta, dcolsum, rows, D, stream);
+    if (D <= 768) return launch_bwd<3>(dy, x, gamma, mean, rstd, dres, dx, dgamma, dbeta, dcolsum, rows, D, stream);
+    return launch_bwd<4>(dy, x, gamma, mean, rstd, dres, dx, dgamma, dbeta, dcolsum, rows, D, stream);
+}

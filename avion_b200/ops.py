@@ -1,0 +1,259 @@
+"""Tensor-level wrappers of the C-ABI kernels (one function per entry point of include/avion_b200.h).
+
+PyTorch is used only for device memory and streams.  Every function launches on torch's current CUDA stream.
+"""
+import ctypes as C
+
+import torch
+
+from . import _lib
+from ._lib import (EPI_BIAS, EPI_BIAS_GELU, EPI_BIAS_GELU_DUAL, EPI_BIAS_RESIDUAL, EPI_DGELU, EPI_F32_ADD, EPI_NONE,
+                   GEMM_NN, GEMM_NT, GEMM_TN, GemmDesc)
+
+bf16, f32 = torch.bfloat16, torch.float32
+_checked_devices = set()
+
+
+def _stream(t):
+    dev = t.device
+    if dev.type != "cuda":
+        raise RuntimeError("avion_b200 kernels run on CUDA (sm_100a) tensors only; got a %s tensor" % dev.type)
+    if dev.index not in _checked_devices:
+        with torch.cuda.device(dev):
+            _lib.call("avn_device_check")
+        _checked_devices.add(dev.index)
+    return C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+
+
+def _p(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+
+
+def _chk(t, dtype, name):
+    if t.dtype != dtype or not t.is_contiguous():
+        raise RuntimeError(f"{name}: expected contiguous {dtype}, got {t.dtype} contiguous={t.is_contiguous()}")
+
+
+# ---------------------------------------------------------------------------------------------------------------
+def sample_rrc_boxes(seed, n, src_w, src_h, scale=(0.5, 1.0), ratio=(3.0 / 4.0, 4.0 / 3.0), hflip_prob=0.0):
+    """Host sampler (decord RRC arithmetic, explicit seed) -> int32 CPU tensor [n,5] = x, y, w, h, hflip."""
+    out = torch.empty(n, 5, dtype=torch.int32)
+    _lib.call("avn_sample_rrc_boxes", seed, n, src_w, src_h, scale[0], scale[1], ratio[0], ratio[1], hflip_prob, _p(out))
+    return out
+
+
+def clip_transform(frames_u8, crop, patch, mean, std, boxes=None, out=None):
+    """uint8 [B,T,Hs,Ws,3] -> bf16 patches [B, T*(crop/patch)^2, 3*patch^2]."""
+    _chk(frames_u8, torch.uint8, "frames")
+    B, T, Hs, Ws, ch = frames_u8.shape
+    assert ch == 3
+    g = crop // patch
+    if out is None:
+        out = torch.empty(B, T * g * g, 3 * patch * patch, dtype=bf16, device=frames_u8.device)
+    if boxes is not None:
+        _chk(boxes, torch.int32, "boxes")
+        assert boxes.shape == (B, 3) and boxes.device == frames_u8.device
+    m = (C.c_float * 3)(*[float(v) for v in mean])
+    s = (C.c_float * 3)(*[float(v) for v in std])
+    _lib.call("avn_clip_transform_u8_bf16", _p(frames_u8), _p(out), B, T, Hs, Ws, crop, patch, _p(boxes), m, s, _stream(frames_u8))
+    return out
+
+
+def layernorm_fwd(x, gamma, beta, eps, out=None, save_stats=True):
+    _chk(x, bf16, "x"); _chk(gamma, f32, "gamma"); _chk(beta, f32, "beta")
+    D = x.shape[-1]
+    rows = x.numel() // D
+    y = out if out is not None else torch.empty_like(x)
+    mean = rstd = None
+    if save_stats:
+        mean = torch.empty(rows, dtype=f32, device=x.device)
+        rstd = torch.empty(rows, dtype=f32, device=x.device)
+    _lib.call("avn_layernorm_fwd", _p(x), _p(gamma), _p(beta), _p(y), _p(mean), _p(rstd), rows, D, float(eps), _stream(x))
+    return y, mean, rstd
+
+
+def layernorm_bwd(dy, x, gamma, mean, rstd, dgamma, dbeta, dres=None, dcolsum=None, out=None):
+    _chk(dy, bf16, "dy"); _chk(x, bf16, "x")
+    D = x.shape[-1]
+    rows = x.numel() // D
+    dx = out if out is not None else torch.empty_like(x)
+    _lib.call("avn_layernorm_bwd", _p(dy), _p(x), _p(gamma), _p(mean), _p(rstd), _p(dres), _p(dx), _p(dgamma), _p(dbeta),
+              _p(dcolsum), rows, D, _stream(x))
+    return dx
+
+
+def gemm(mode, epi, M, N, K, A, lda, B, ldb, Cm, ldc, batch=1, a_bs=0, b_bs=0, c_bs=0, C2=None, bias=None, R=None, ldr=0,
+         r_bs=0, splits=1):
+    """Raw descriptor-level GEMM (see include/avion_b200.h); A/B/Cm/C2/R are tensors whose data_ptr is the origin."""
+    d = GemmDesc(mode, epi, M, N, K, batch, A.data_ptr(), lda, a_bs, B.data_ptr(), ldb, b_bs, Cm.data_ptr(), ldc, c_bs,
+                 C2.data_ptr() if C2 is not None else None, bias.data_ptr() if bias is not None else None,
+                 R.data_ptr() if R is not None else None, ldr, r_bs, splits)
+    _lib.call("avn_gemm_bf16", C.byref(d), _stream(A))
+
+
+def linear_fwd(x, w, bias=None, epi=EPI_NONE, residual=None, out=None, out2=None):
+    """y[M,N] = epi(x[M,K] @ w[N,K]^T); x,w bf16; bias fp32."""
+    _chk(x, bf16, "x"); _chk(w, bf16, "w")
+    K = x.shape[-1]
+    M = x.numel() // K
+    N = w.shape[0]
+    y = out if out is not None else torch.empty(*x.shape[:-1], N, dtype=bf16, device=x.device)
+    if epi == EPI_BIAS_GELU_DUAL and out2 is None:
+        out2 = torch.empty_like(y)
+    gemm(GEMM_NT, epi, M, N, K, x, K, w, K, y, N, C2=out2, bias=bias, R=residual, ldr=N)
+    return (y, out2) if epi == EPI_BIAS_GELU_DUAL else y
+
+
+def linear_dgrad(dy, w, epi=EPI_NONE, pre=None, out=None):
+    """dx[M,K] = epi(dy[M,N] @ w[N,K]); with EPI_DGELU: dx *= gelu'(pre[M,K])."""
+    _chk(dy, bf16, "dy"); _chk(w, bf16, "w")
+    N, K = w.shape
+    M = dy.numel() // N
+    dx = out if out is not None else torch.empty(*dy.shape[:-1], K, dtype=bf16, device=dy.device)
+    gemm(GEMM_NN, epi, M, K, N, dy, N, w, K, dx, K, R=pre, ldr=K)
+    return dx
+
+
+def _wgrad_splits(tokens, M, N, device):
+    sms = torch.cuda.get_device_properties(device).multi_processor_count
+    tiles = ((M + 127) // 128) * ((N + 255) // 256 if N % 256 == 0 else (N + 127) // 128)
+    kblocks = (tokens + 63) // 64
+    return max(1, min(kblocks, (2 * sms + tiles - 1) // tiles))
+
+
+def linear_wgrad(dy, x, dw):
+    """dw[N,K] (fp32) += dy[tok,N]^T @ x[tok,K]."""
+    _chk(dy, bf16, "dy"); _chk(x, bf16, "x"); _chk(dw, f32, "dw")
+    N, K = dw.shape
+    tok = dy.numel() // N
+    gemm(GEMM_TN, EPI_F32_ADD, N, K, tok, dy, N, x, K, dw, K, splits=_wgrad_splits(tok, N, K, dy.device))
+    return dw
+
+
+def attn_fwd(qkv, heads, scale, causal=False, out=None):
+    """qkv bf16 [B,S,3*H*64] -> out bf16 [B,S,H*64], lse fp32 [B,H,S]."""
+    _chk(qkv, bf16, "qkv")
+    B, S, W3 = qkv.shape
+    assert W3 == 3 * heads * 64, "head dim must be 64"
+    o = out if out is not None else torch.empty(B, S, heads * 64, dtype=bf16, device=qkv.device)
+    lse = torch.empty(B, heads, S, dtype=f32, device=qkv.device)
+    _lib.call("avn_attn_fwd", _p(qkv), _p(o), _p(lse), B, S, heads, float(scale), int(causal), _stream(qkv))
+    return o, lse
+
+
+def attn_bwd(qkv, o, do, lse, heads, scale, causal=False, dqkv=None, dq_acc=None):
+    _chk(qkv, bf16, "qkv"); _chk(o, bf16, "o"); _chk(do, bf16, "do"); _chk(lse, f32, "lse")
+    B, S, _ = qkv.shape
+    if dqkv is None:
+        dqkv = torch.empty_like(qkv)
+    delta = torch.empty(B, heads, S, dtype=f32, device=qkv.device)
+    if dq_acc is None:
+        dq_acc = torch.empty(B, S, heads * 64, dtype=f32, device=qkv.device)
+    _lib.call("avn_attn_bwd", _p(qkv), _p(o), _p(do), _p(lse), _p(dqkv), _p(delta), _p(dq_acc), B, S, heads, float(scale),
+              int(causal), _stream(qkv))
+    return dqkv
+
+
+def cast_bf16(src, out=None):
+    _chk(src, f32, "src")
+    dst = out if out is not None else torch.empty(src.shape, dtype=bf16, device=src.device)
+    _lib.call("avn_cast_f32_bf16", _p(src), _p(dst), src.numel(), _stream(src))
+    return dst
+
+
+def transpose_cast_bf16(src):
+    _chk(src, f32, "src")
+    r, c = src.shape
+    dst = torch.empty(c, r, dtype=bf16, device=src.device)
+    _lib.call("avn_transpose_cast_f32_bf16", _p(src), _p(dst), r, c, _stream(src))
+    return dst
+
+
+def colsum(x, out):
+    """out[N] (fp32) += column sums of x bf16 [rows,N]."""
+    _chk(x, bf16, "x"); _chk(out, f32, "out")
+    N = x.shape[-1]
+    _lib.call("avn_colsum_bf16", _p(x), N, _p(out), x.numel() // N, N, _stream(x))
+    return out
+
+
+def pos_table_fwd(cls, pos, temporal, T, G):
+    D = cls.numel()
+    table = torch.empty(T * G + 1, D, dtype=bf16, device=cls.device)
+    _lib.call("avn_pos_table_fwd", _p(cls), _p(pos), _p(temporal), _p(table), T, G, D, _stream(cls))
+    return table
+
+
+def broadcast_row(x, row, B, batch_stride, D):
+    _lib.call("avn_broadcast_row", _p(x), _p(row), B, batch_stride, D, _stream(x))
+
+
+def pos_table_bwd(dx, dcls, dpos, dtemporal, T, G):
+    B, S, D = dx.shape
+    ws = torch.empty(S, D, dtype=f32, device=dx.device)
+    _lib.call("avn_pos_table_bwd", _p(dx), _p(ws), _p(dcls), _p(dpos), _p(dtemporal), B, T, G, D, _stream(dx))
+
+
+def token_embed_fwd(ids, tok_emb, pos):
+    _chk(ids, torch.int64, "ids"); _chk(tok_emb, f32, "tok_emb"); _chk(pos, f32, "pos")
+    B, L = ids.shape
+    D = tok_emb.shape[1]
+    x = torch.empty(B, L, D, dtype=bf16, device=ids.device)
+    _lib.call("avn_token_embed_fwd", _p(ids), _p(tok_emb), _p(pos), _p(x), B, L, D, _stream(x))
+    return x
+
+
+def token_embed_bwd(ids, dx, dtok, dpos):
+    B, L, D = dx.shape
+    _lib.call("avn_token_embed_bwd", _p(ids), _p(dx), _p(dtok), _p(dpos), B, L, D, _stream(dx))
+
+
+def head_fwd(x2d, row_idx, gamma, beta, proj, eps):
+    """x2d bf16 [rows,D]; row_idx int64 [n] -> emb fp32 [n,E] (L2-normalised) + saved (u, mean, rstd)."""
+    _chk(x2d, bf16, "x"); _chk(row_idx, torch.int64, "row_idx"); _chk(proj, f32, "proj")
+    n = row_idx.numel()
+    D, E = proj.shape
+    dev = x2d.device
+    emb = torch.empty(n, E, dtype=f32, device=dev)
+    u = torch.empty(n, E, dtype=f32, device=dev)
+    mean = torch.empty(n, dtype=f32, device=dev)
+    rstd = torch.empty(n, dtype=f32, device=dev)
+    _lib.call("avn_head_fwd", _p(x2d), _p(row_idx), _p(gamma), _p(beta), _p(proj), _p(emb), _p(u), _p(mean), _p(rstd), n, D, E,
+              float(eps), _stream(x2d))
+    return emb, (u, mean, rstd)
+
+
+def head_bwd(demb, x2d, row_idx, gamma, beta, proj, saved, dx2d, dgamma, dbeta, dproj):
+    u, mean, rstd = saved
+    n = row_idx.numel()
+    D, E = proj.shape
+    ws = torch.empty(n, D + E, dtype=f32, device=x2d.device)
+    _chk(demb, f32, "demb")
+    _lib.call("avn_head_bwd", _p(demb), _p(x2d), _p(row_idx), _p(gamma), _p(beta), _p(proj), _p(u), _p(mean), _p(rstd), _p(dx2d),
+              _p(dgamma), _p(dbeta), _p(dproj), _p(ws), n, D, E, _stream(x2d))
+
+
+def infonce_fwd(img, txt, all_img, all_txt, scale, row_offset):
+    """-> (lse [2,n], out [2] = (sum of per-row (CE_i+CE_t)/2, number of correct image->text argmaxes))."""
+    for t, nm in ((img, "img"), (txt, "txt"), (all_img, "all_img"), (all_txt, "all_txt")):
+        _chk(t, f32, nm)
+    n, E = img.shape
+    N = all_img.shape[0]
+    lse = torch.empty(2, n, dtype=f32, device=img.device)
+    out = torch.zeros(2, dtype=f32, device=img.device)
+    _lib.call("avn_infonce_fwd", _p(img), _p(txt), _p(all_img), _p(all_txt), float(scale), n, N, E, row_offset, _p(lse), _p(out),
+              _stream(img))
+    return lse, out
+
+
+def infonce_bwd(img, txt, all_img, all_txt, scale, row_offset, lse, gscale):
+    """-> (d_all fp32 [2,N,E] (image block, text block), dscale fp32 [1])."""
+    n, E = img.shape
+    N = all_img.shape[0]
+    dev = img.device
+    dlogits = torch.empty(2, n, N, dtype=f32, device=dev)
+    d_all = torch.zeros(2, N, E, dtype=f32, device=dev)
+    dscale = torch.zeros(1, dtype=f32, device=dev)
+    _lib.call("avn_infonce_bwd", _p(img), _p(txt), _p(all_img), _p(all_txt), float(scale), n, N, E, row_offset, _p(lse),
+              float(gscale), _p(dlogits), _p(d_all), _p(dscale), _stream(img))
+    return d_all, dscale

@@ -1,0 +1,229 @@
+"""Per-kernel parity on the B200: every C-ABI kernel against a plain fp32 PyTorch statement of the same arithmetic
+(and the oracle where one exists).  Integer/byte work is checked bit-exactly; floating point within stated tolerances."""
+import math
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+from oracle import clip_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+bf16, f32 = torch.bfloat16, torch.float32
+
+
+@pytest.fixture(scope="module")
+def ops():
+    from avion_b200 import ops as _ops
+    return _ops
+
+
+def rnd(*shape, scale=1.0, dtype=bf16, seed=None):
+    g = torch.Generator(device="cuda")
+    g.manual_seed(seed if seed is not None else (hash(shape) & 0xffff))
+    return (torch.randn(*shape, generator=g, device="cuda", dtype=f32) * scale).to(dtype)
+
+
+def rel_err(a, b):
+    a, b = a.float(), b.float()
+    return float((a - b).norm() / (b.norm() + 1e-12))
+
+
+# ---------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("shape", [(2, 4, 64, 64, 16), (3, 2, 224, 224, 16), (1, 1, 96, 96, 32)])
+def test_clip_transform_bit_exact(ops, shape):
+    B, T, H, W, p = shape
+    clips = torch.from_numpy(np.random.RandomState(1).randint(0, 256, (B, T, H, W, 3)).astype(np.uint8))
+    ref = O.patchify(O.clip_transform(clips), p).to(bf16)
+    got = ops.clip_transform(clips.cuda(), H, p, O.MEAN_OPENAI, O.STD_OPENAI)
+    assert torch.equal(got.cpu(), ref)
+
+
+def test_clip_transform_crop_flip_bit_exact(ops):
+    B, T, Hs, Ws, crop, p = 4, 3, 101, 157, 64, 16
+    clips = torch.from_numpy(np.random.RandomState(2).randint(0, 256, (B, T, Hs, Ws, 3)).astype(np.uint8))
+    boxes = torch.tensor([[0, 0, 0], [93, 37, 1], [5, 11, 0], [92, 36, 1]], dtype=torch.int32)
+    ref = O.patchify(O.clip_transform(O.crop_clip(clips, boxes, (crop, crop))), p).to(bf16)
+    got = ops.clip_transform(clips.cuda(), crop, p, O.MEAN_OPENAI, O.STD_OPENAI, boxes=boxes.cuda())
+    assert torch.equal(got.cpu(), ref)
+
+
+@pytest.mark.parametrize("rows,D", [(1000, 768), (77 * 3, 512), (65 * 6, 128), (50, 1024)])
+def test_layernorm_fwd_bwd(ops, rows, D):
+    x = rnd(rows, D, seed=1)
+    g = (1 + 0.1 * torch.randn(D, device="cuda")).float()
+    b = (0.1 * torch.randn(D, device="cuda")).float()
+    y, mean, rstd = ops.layernorm_fwd(x, g, b, 1e-6)
+    xr = x.float().requires_grad_(True)
+    gr, br = g.clone().requires_grad_(True), b.clone().requires_grad_(True)
+    yr = F.layer_norm(xr, (D,), gr, br, 1e-6)
+    assert rel_err(y, yr) < 4e-3
+    dy = rnd(rows, D, seed=2)
+    dres = rnd(rows, D, seed=3)
+    yr.backward(dy.float())
+    dg, db, dc = (torch.zeros(D, device="cuda") for _ in range(3))
+    dx = ops.layernorm_bwd(dy, x, g, mean, rstd, dg, db, dres=dres, dcolsum=dc)
+    assert rel_err(dx, xr.grad + dres.float()) < 5e-3
+    assert rel_err(dg, gr.grad) < 2e-3 and rel_err(db, br.grad) < 2e-3
+    assert rel_err(dc, dx.float().sum(0)) < 1e-4
+
+
+GEMM_SHAPES = [(256, 256, 128), (1000, 768, 768), (130, 384, 128), (2304, 3072, 768), (128 * 150, 768, 3072), (300, 200, 72)]
+
+
+@pytest.mark.parametrize("M,N,K", GEMM_SHAPES)
+def test_gemm_nt_epilogues(ops, M, N, K):
+    x, w = rnd(M, K, seed=1), rnd(N, K, scale=K ** -0.5, seed=2)
+    bias = torch.randn(N, device="cuda")
+    res = rnd(M, N, seed=3)
+    acc = x.float() @ w.float().T
+    assert rel_err(ops.linear_fwd(x, w), acc) < 4e-3
+    assert rel_err(ops.linear_fwd(x, w, bias, ops.EPI_BIAS), acc + bias) < 4e-3
+    assert rel_err(ops.linear_fwd(x, w, bias, ops.EPI_BIAS_GELU), F.gelu(acc + bias)) < 5e-3
+    h, pre = ops.linear_fwd(x, w, bias, ops.EPI_BIAS_GELU_DUAL)
+    assert rel_err(pre, acc + bias) < 4e-3 and rel_err(h, F.gelu(acc + bias)) < 5e-3
+    assert rel_err(ops.linear_fwd(x, w, bias, ops.EPI_BIAS_RESIDUAL, residual=res), acc + bias + res.float()) < 4e-3
+
+
+@pytest.mark.parametrize("M,N,K", GEMM_SHAPES)
+def test_gemm_nn_dgrad(ops, M, N, K):
+    dy, w = rnd(M, N, seed=4), rnd(N, K, scale=N ** -0.5, seed=5)
+    ref = dy.float() @ w.float()
+    assert rel_err(ops.linear_dgrad(dy, w), ref) < 4e-3
+    pre = rnd(M, K, seed=6)
+    p32 = pre.float().requires_grad_(True)
+    F.gelu(p32).sum().backward()
+    assert rel_err(ops.linear_dgrad(dy, w, ops.EPI_DGELU, pre=pre), ref * p32.grad) < 5e-3
+
+
+@pytest.mark.parametrize("tok,N,K", [(512, 256, 128), (1000, 768, 768), (77 * 9, 384, 128), (128 * 150, 2304, 768), (333, 200, 72)])
+def test_gemm_tn_wgrad(ops, tok, N, K):
+    dy, x = rnd(tok, N, seed=7), rnd(tok, K, seed=8)
+    dw = torch.ones(N, K, device="cuda")
+    ops.linear_wgrad(dy, x, dw)
+    assert rel_err(dw, 1 + dy.float().T @ x.float()) < 3e-3
+
+
+def test_gemm_batched_patch_embed_layout(ops):
+    """Patch-embed geometry: A [B][P][K] -> C rows 1.. of [B][P+1][D] with a shared residual table."""
+    B, P, K, D = 3, 196, 256, 384
+    a, w = rnd(B, P, K, seed=1), rnd(D, K, scale=K ** -0.5, seed=2)
+    table = rnd(P + 1, D, seed=3)
+    x = torch.zeros(B, P + 1, D, dtype=bf16, device="cuda")
+    ops.gemm(ops.GEMM_NT, ops.EPI_BIAS_RESIDUAL, P, D, K, a, K, w, K, x[:, 1:], D, batch=B, a_bs=P * K, c_bs=(P + 1) * D,
+             R=table[1:], ldr=D, r_bs=0)
+    ref = a.float() @ w.float().T + table[1:].float()
+    assert rel_err(x[:, 1:], ref) < 4e-3
+    assert float(x[:, 0].abs().max()) == 0.0
+    dw = torch.zeros(D, K, device="cuda")
+    ops.gemm(ops.GEMM_TN, ops.EPI_F32_ADD, D, K, P, x[:, 1:], D, a, K, dw, K, batch=B, a_bs=(P + 1) * D, b_bs=P * K, splits=5)
+    assert rel_err(dw, torch.einsum("bpd,bpk->dk", x[:, 1:].float(), a.float())) < 3e-3
+
+
+def attn_ref(qkv, H, scale, causal):
+    B, S, _ = qkv.shape
+    q, k, v = (t.transpose(1, 2) for t in qkv.float().view(B, S, 3, H, 64).unbind(2))
+    s = (q @ k.transpose(-1, -2)) * scale
+    if causal:
+        s = s + torch.full((S, S), float("-inf"), device=qkv.device).triu_(1)
+    lse = torch.logsumexp(s, -1)
+    o = (torch.softmax(s, -1) @ v).transpose(1, 2).reshape(B, S, H * 64)
+    return o, lse
+
+
+@pytest.mark.parametrize("B,S,H,causal", [(2, 128, 2, False), (2, 65, 2, False), (3, 785, 3, False), (1, 3137, 2, False),
+                                          (4, 77, 2, True), (2, 300, 2, True), (2, 256, 1, False)])
+def test_attention_fwd_bwd(ops, B, S, H, causal):
+    qkv = rnd(B, S, 3 * H * 64, seed=11)
+    scale = 0.125
+    o, lse = ops.attn_fwd(qkv, H, scale, causal)
+    q32 = qkv.float().requires_grad_(True)
+    o_ref, lse_ref = attn_ref(q32, H, scale, causal)
+    assert rel_err(o, o_ref) < 6e-3
+    assert float((lse - lse_ref).abs().max()) < 2e-3
+    do = rnd(B, S, H * 64, seed=12)
+    o_ref.backward(do.float())
+    dqkv = ops.attn_bwd(qkv, o, do, lse, H, scale, causal)
+    g = q32.grad.view(B, S, 3, H * 64)
+    d = dqkv.view(B, S, 3, H * 64)
+    for i, name in enumerate("qkv"):
+        assert rel_err(d[:, :, i], g[:, :, i]) < 1.5e-2, name
+
+
+def test_cast_transpose_colsum(ops):
+    w = torch.randn(300, 136, device="cuda")
+    assert torch.equal(ops.cast_bf16(w), w.to(bf16))
+    assert torch.equal(ops.transpose_cast_bf16(w), w.T.contiguous().to(bf16))
+    x = rnd(5000, 384, seed=1)
+    out = torch.ones(384, device="cuda")
+    ops.colsum(x, out)
+    assert rel_err(out, 1 + x.float().sum(0)) < 1e-5
+
+
+def test_pos_table_and_token_embed(ops):
+    T, G, D, B = 4, 16, 128, 3
+    cls, pos, tmp = torch.randn(D, device="cuda"), torch.randn(G + 1, D, device="cuda"), torch.randn(T, D, device="cuda")
+    table = ops.pos_table_fwd(cls, pos, tmp, T, G)
+    ref = torch.cat([(cls + pos[0])[None], pos[1:].repeat(T, 1) + tmp.repeat_interleave(G, 0)])
+    assert torch.equal(table, ref.to(bf16))
+    dx = rnd(B, T * G + 1, D, seed=5)
+    dcls, dpos, dtmp = torch.zeros(D, device="cuda"), torch.zeros(G + 1, D, device="cuda"), torch.zeros(T, D, device="cuda")
+    ops.pos_table_bwd(dx, dcls, dpos, dtmp, T, G)
+    s = dx.float().sum(0)
+    assert rel_err(dcls, s[0]) < 1e-5 and rel_err(dpos[0], s[0]) < 1e-5
+    assert rel_err(dpos[1:], s[1:].view(T, G, D).sum(0)) < 1e-5
+    assert rel_err(dtmp, s[1:].view(T, G, D).sum(1)) < 1e-5
+    ids = torch.randint(0, 50, (B, 77), device="cuda")
+    emb, p = torch.randn(50, D, device="cuda"), torch.randn(77, D, device="cuda")
+    x = ops.token_embed_fwd(ids, emb, p)
+    assert torch.equal(x, (emb[ids] + p).to(bf16))
+    dxe = rnd(B, 77, D, seed=6)
+    demb, dp = torch.zeros_like(emb), torch.zeros_like(p)
+    ops.token_embed_bwd(ids, dxe, demb, dp)
+    ref = torch.zeros_like(emb).index_add_(0, ids.view(-1), dxe.float().view(-1, D))
+    assert rel_err(demb, ref) < 1e-5 and rel_err(dp, dxe.float().sum(0)) < 1e-5
+
+
+def test_head_fwd_bwd(ops):
+    rows, D, E, n = 500, 768, 256, 37
+    x = rnd(rows, D, seed=1)
+    idx = torch.randperm(rows, device="cuda")[:n].contiguous()
+    g, b = (1 + 0.1 * torch.randn(D, device="cuda")), 0.1 * torch.randn(D, device="cuda")
+    proj = torch.randn(D, E, device="cuda") * D ** -0.5
+    emb, saved = ops.head_fwd(x, idx, g, b, proj, 1e-6)
+    xr = x.float().requires_grad_(True)
+    gr, br, pr = (t.clone().requires_grad_(True) for t in (g, b, proj))
+    ref = F.normalize(F.layer_norm(xr[idx], (D,), gr, br, 1e-6) @ pr, dim=-1)
+    assert rel_err(emb, ref) < 1e-5
+    demb = torch.randn(n, E, device="cuda")
+    ref.backward(demb)
+    dx = torch.zeros(rows, D, dtype=bf16, device="cuda")
+    dg, db, dp = torch.zeros(D, device="cuda"), torch.zeros(D, device="cuda"), torch.zeros(D, E, device="cuda")
+    ops.head_bwd(demb, x, idx, g, b, proj, saved, dx, dg, db, dp)
+    assert rel_err(dx, xr.grad) < 5e-3
+    assert rel_err(dg, gr.grad) < 1e-4 and rel_err(db, br.grad) < 1e-4 and rel_err(dp, pr.grad) < 1e-4
+
+
+@pytest.mark.parametrize("n,N,E,off", [(6, 6, 64, 0), (32, 128, 64, 64), (256, 2048, 256, 512), (5, 20, 64, 15)])
+def test_infonce_fwd_bwd(ops, n, N, E, off):
+    torch.manual_seed(0)
+    all_img = F.normalize(torch.randn(N, E, device="cuda"), dim=-1)
+    all_txt = F.normalize(all_img + 0.7 * torch.randn(N, E, device="cuda"), dim=-1)
+    scale = 14.3
+    ai, at = all_img.clone().requires_grad_(True), all_txt.clone().requires_grad_(True)
+    sc = torch.tensor(scale, device="cuda", requires_grad=True)
+    img, txt = ai[off:off + n], at[off:off + n]
+    li, lt = sc * img @ at.T, sc * txt @ ai.T
+    labels = torch.arange(n, device="cuda") + off
+    loss = (F.cross_entropy(li, labels) + F.cross_entropy(lt, labels)) / 2
+    correct = (li.argmax(-1) == labels).sum()
+    loss.backward()
+    lse, out = ops.infonce_fwd(all_img[off:off + n].contiguous(), all_txt[off:off + n].contiguous(), all_img, all_txt, scale, off)
+    assert abs(float(out[0]) / n - float(loss)) < 1e-4 * max(1.0, abs(float(loss)))
+    assert int(out[1]) == int(correct)
+    d_all, dscale = ops.infonce_bwd(all_img[off:off + n].contiguous(), all_txt[off:off + n].contiguous(), all_img, all_txt, scale,
+                                    off, lse, 1.0)
+    assert rel_err(d_all[0], ai.grad) < 1e-4 and rel_err(d_all[1], at.grad) < 1e-4
+    assert abs(float(dscale) - float(sc.grad)) < 1e-4 * max(1.0, abs(float(sc.grad)))
