@@ -44,7 +44,7 @@ SIGNATURES = {
     "avn_token_embed_fwd": [_vp, _vp, _vp, _vp, _i, _i, _i, _vp],
     "avn_token_embed_bwd": [_vp, _vp, _vp, _vp, _i, _i, _i, _vp],
     "avn_head_fwd": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _f, _vp],
-    "avn_head_bwd": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp],
+    "avn_head_bwd": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp],
     "avn_infonce_fwd": [_vp, _vp, _vp, _vp, _f, _i, _i, _i, _i, _vp, _vp, _vp],
     "avn_infonce_bwd": [_vp, _vp, _vp, _vp, _f, _i, _i, _i, _i, _vp, _f, _vp, _vp, _vp, _vp],
 }

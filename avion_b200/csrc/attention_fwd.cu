@@ -160,6 +160,22 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
                 }
                 const float m_new = fmaxf(m, mx * scale_log2);
                 const float alpha = exp2f(m - m_new);
+                // fold the previous tile's P*V into the register accumulator, then rescale to the new maximum
+                // (waiting for P*V of tile j-1 here also guarantees that the MMA has finished READING this group's P
+                //  buffer, which pass 2 is about to overwrite)
+                if (j > 0) {
+                    mbar_wait(&bars->o_full[w], (j - 1) & 1);
+                    tc_fence_after();
+#pragma unroll
+                    for (int c = 0; c < 2; ++c) {
+                        uint32_t v[32];
+                        tmem_ld32(t_o + c * 32, v);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) o[c * 32 + i] = (o[c * 32 + i] + __uint_as_float(v[i])) * alpha;
+                    }
+                    tc_fence_before();
+                }
                 // pass 2: probabilities -> bf16 -> smem (two K-major 128B-swizzled [128][64] sub-tiles)
                 float rs = 0.f;
 #pragma unroll
@@ -188,20 +204,6 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
                 l = fmaf(l, alpha, rs);
                 m = m_new;
                 fence_proxy_async_smem();
-                // fold the previous tile's P*V into the register accumulator, then rescale to the new maximum
-                if (j > 0) {
-                    mbar_wait(&bars->o_full[w], (j - 1) & 1);
-                    tc_fence_after();
-#pragma unroll
-                    for (int c = 0; c < 2; ++c) {
-                        uint32_t v[32];
-                        tmem_ld32(t_o + c * 32, v);
-                        tmem_ld_wait();
-#pragma unroll
-                        for (int i = 0; i < 32; ++i) o[c * 32 + i] = (o[c * 32 + i] + __uint_as_float(v[i])) * alpha;
-                    }
-                    tc_fence_before();
-                }
                 mbar_arrive(&bars->p_ready[w]);
             }
             // last tile's P*V

@@ -57,7 +57,7 @@ __global__ void __launch_bounds__(256)
 head_bwd_row_kernel(const float* __restrict__ demb, const __nv_bfloat16* __restrict__ x, const int64_t* __restrict__ row_idx,
                     const float* __restrict__ gamma, const float* __restrict__ proj, const float* __restrict__ u,
                     const float* __restrict__ mean_in, const float* __restrict__ rstd_in, __nv_bfloat16* __restrict__ dx,
-                    float* __restrict__ dgamma, float* __restrict__ dbeta, float* __restrict__ ws, int D, int E) {
+                    float* __restrict__ dgamma, float* __restrict__ dbeta, float* __restrict__ ws, int D, int E, int normalized) {
     extern __shared__ float sm[];
     float* du = sm;            // [E]
     float* dyv = sm + E;       // [D]
@@ -75,7 +75,7 @@ head_bwd_row_kernel(const float* __restrict__ demb, const __nv_bfloat16* __restr
     const float norm = fmaxf(sqrtf(n2), 1e-12f);
     for (int e = threadIdx.x; e < E; e += blockDim.x) {
         const float uu = u[(long long)i * E + e];
-        const float v = (demb[(long long)i * E + e] - uu * dot / (norm * norm)) / norm;
+        const float v = normalized ? (demb[(long long)i * E + e] - uu * dot / (norm * norm)) / norm : demb[(long long)i * E + e];
         du[e] = v; du_ws[e] = v;
     }
     __syncthreads();
@@ -129,13 +129,13 @@ extern "C" int avn_head_fwd(const void* x, const int64_t* row_idx, const float* 
 
 extern "C" int avn_head_bwd(const float* demb, const void* x, const int64_t* row_idx, const float* gamma, const float* beta,
                             const float* proj, const float* u, const float* mean, const float* rstd, void* dx, float* dgamma,
-                            float* dbeta, float* dproj, float* ws, int n, int D, int E, avn_stream_t stream_) {
+                            float* dbeta, float* dproj, float* ws, int n, int D, int E, int normalized, avn_stream_t stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
     AVN_REQUIRE(demb && x && row_idx && gamma && beta && proj && u && mean && rstd && dx && dgamma && dbeta && dproj && ws, "head_bwd: null pointer");
     AVN_REQUIRE(n > 0 && D > 0 && E > 0, "head_bwd: bad sizes");
     const size_t smem = (size_t)(E + D + 8) * sizeof(float);
     head_bwd_row_kernel<<<n, 256, smem, stream>>>(demb, (const __nv_bfloat16*)x, row_idx, gamma, proj, u, mean, rstd,
-                                                  (__nv_bfloat16*)dx, dgamma, dbeta, ws, D, E);
+                                                  (__nv_bfloat16*)dx, dgamma, dbeta, ws, D, E, normalized);
     AVN_CHECK_CUDA(cudaGetLastError());
     const long long tot = (long long)D * E;
     head_bwd_proj_kernel<<<(int)((tot + 255) / 256), 256, 0, stream>>>(ws, gamma, beta, dproj, n, D, E);

@@ -1,0 +1,29 @@
+"""GPU-side clip transform: the fused replacement of Permute + kornia Normalize (+ the model's patchify)
+(scripts/main_lavila_pretrain.py:425-435,816-817; avion/data/transforms.py:10-26; avion/models/transformer.py:319)."""
+import torch
+import torch.nn as nn
+
+from .. import ops
+
+MEAN_OPENAI = (108.3272985, 116.7460125, 104.09373615000001)
+STD_OPENAI = (68.5005327, 66.6321579, 70.32316305)
+MEAN_TIMM = (0.485 * 255, 0.456 * 255, 0.406 * 255)
+STD_TIMM = (0.229 * 255, 0.224 * 255, 0.225 * 255)
+
+
+class GPUClipTransform(nn.Module):
+    """uint8 decord frames [B,T,Hs,Ws,3] -> bf16 patches [B, T*(crop/patch)^2, 3*patch^2] in one kernel.
+
+    boxes (optional): int32 [B,3] = (x, y, hflip) per clip; use `sample_boxes` for decord-style random crops of a fixed
+    crop x crop window (the resize step of decord's filter graph lives in ffmpeg and is out of scope)."""
+
+    def __init__(self, crop=224, patch=16, mean=MEAN_OPENAI, std=STD_OPENAI):
+        super().__init__()
+        self.crop, self.patch, self.mean, self.std = crop, patch, tuple(mean), tuple(std)
+
+    def forward(self, frames_u8, boxes=None):
+        return ops.clip_transform(frames_u8, self.crop, self.patch, self.mean, self.std, boxes=boxes)
+
+    @staticmethod
+    def sample_boxes(seed, n, src_w, src_h, **kw):
+        return ops.sample_rrc_boxes(seed, n, src_w, src_h, **kw)

@@ -1,0 +1,74 @@
+"""ClipLoss with the reference's constructor and result dict (avion/losses/losses.py:80-149), computed by the sharded
+InfoNCE kernels: each rank evaluates its local rows of both logit matrices against the all-gathered embeddings
+(one packed NCCL all-gather; one reduce-scatter in the backward, as torch.distributed.nn.all_gather does, :55-60)."""
+import torch
+import torch.distributed as dist
+import torch.nn as nn
+
+from .. import ops
+
+
+class _InfoNCEFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, img, txt, scale, rank, world, local_loss, gather_with_grad, group):
+        img32, txt32 = img.detach().float().contiguous(), txt.detach().float().contiguous()
+        n, E = img32.shape
+        if world > 1:
+            packed = torch.stack([img32, txt32])                               # [2,n,E]
+            gathered = torch.empty(world, 2, n, E, dtype=torch.float32, device=img.device)
+            dist.all_gather_into_tensor(gathered, packed, group=group)        # ONE collective for both towers
+            both = gathered.permute(1, 0, 2, 3).reshape(2, world * n, E).contiguous()
+            all_img, all_txt = both[0], both[1]
+        else:
+            all_img, all_txt = img32, txt32
+        s = float(scale.detach())
+        off = rank * n
+        lse, out = ops.infonce_fwd(img32, txt32, all_img, all_txt, s, off)
+        stats = torch.stack([out[0] / n, 100.0 * out[1] / n])                  # rank-local mean loss, top-1 accuracy
+        if world > 1 and not local_loss:
+            # the reference's default mode evaluates the full NxN problem on every rank (:119-123); its scalar is the
+            # mean over all N rows = the mean of the rank-local means
+            dist.all_reduce(stats, op=dist.ReduceOp.SUM, group=group)
+            stats = stats / world
+        ctx.save_for_backward(img32, txt32, all_img, all_txt, lse)
+        ctx.cfg = (s, off, rank, world, local_loss, gather_with_grad, group, img.dtype, txt.dtype)
+        loss, acc = stats[0].clone(), stats[1].clone()
+        ctx.mark_non_differentiable(acc)
+        return loss, acc
+
+    @staticmethod
+    def backward(ctx, gloss, _gacc):
+        img32, txt32, all_img, all_txt, lse = ctx.saved_tensors
+        s, off, rank, world, local_loss, gather_with_grad, group, dt_i, dt_t = ctx.cfg
+        n, E = img32.shape
+        d_all, dscale = ops.infonce_bwd(img32, txt32, all_img, all_txt, s, off, lse, 1.0)
+        if world > 1 and (gather_with_grad or not local_loss):
+            # d_all holds this rank's contribution to every rank's features: sum them where they belong
+            inp = d_all.view(2, world, n, E).permute(1, 0, 2, 3).contiguous()  # [W,2,n,E]
+            local = torch.empty(2, n, E, dtype=torch.float32, device=img32.device)
+            dist.reduce_scatter_tensor(local, inp, op=dist.ReduceOp.SUM, group=group)
+            if not gather_with_grad:
+                local = local / world       # full-matrix loss with constant remote features (:62-72) == 1/W of the sum
+        else:
+            local = d_all[:, off:off + n]
+        g = gloss.float()
+        return ((local[0] * g).to(dt_i), (local[1] * g).to(dt_t), (dscale[0] * g).to(gloss.dtype).reshape(()),
+                None, None, None, None, None)
+
+
+class ClipLoss(nn.Module):
+    def __init__(self, local_loss=False, gather_with_grad=False, cache_labels=False, rank=0, world_size=1, use_horovod=False,
+                 group=None):
+        super().__init__()
+        assert not use_horovod, "horovod is not supported (the reference never enables it either)"
+        self.local_loss = local_loss
+        self.gather_with_grad = gather_with_grad
+        self.cache_labels = cache_labels          # labels are implicit (row_offset + r) in the kernel
+        self.rank = rank
+        self.world_size = world_size
+        self.group = group
+
+    def forward(self, image_features, text_features, logit_scale):
+        loss, acc = _InfoNCEFn.apply(image_features, text_features, logit_scale, self.rank, self.world_size, self.local_loss,
+                                     self.gather_with_grad, self.group)
+        return {"loss": loss, "clip_acc": acc}

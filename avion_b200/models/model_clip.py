@@ -1,0 +1,71 @@
+"""CLIP wrapper + factories with the reference's names and signatures (avion/models/model_clip.py:41-341)."""
+import numpy as np
+import torch
+import torch.nn as nn
+
+from .transformer import TextTransformer, VisionTransformer
+
+
+class CLIP(nn.Module):
+    """avion/models/model_clip.py:41-99.  forward(image, text) -> (image_embed, text_embed, logit_scale.exp()), both
+    embeddings L2-normalised.  `image` may be uint8 clips [B,T,H,W,3] (fused transform entry), bf16 patches, or the
+    reference's normalised float [B,3,T,H,W]."""
+
+    def __init__(self, embed_dim: int, vision_model: nn.Module, text_model: nn.Module, vision_width: int = None,
+                 text_width: int = None, freeze_temperature=False, **kwargs):
+        super().__init__()
+        assert vision_width is None and text_width is None, \
+            "extra CLIP-level projections are unused by every AVION factory (model_clip.py:143-148) and not implemented"
+        self.visual = vision_model
+        self.textual = text_model
+        self.logit_scale = nn.Parameter(torch.ones([]) * np.log(1 / 0.07))
+        if freeze_temperature:
+            self.logit_scale.requires_grad_(False)
+        self.image_projection = None
+        self.text_projection = None
+
+    def encode_image(self, image):
+        return self.visual(image)
+
+    def encode_text(self, text, cast_dtype=None):
+        return self.textual(text, cast_dtype=cast_dtype)
+
+    def forward(self, image, text):
+        # F.normalize is fused into the head kernel of each tower
+        return (self.visual.forward_normalized(image), self.textual.forward_normalized(text), self.logit_scale.exp())
+
+
+def _build(vision_kw, text_kw, project_embed_dim, freeze_temperature, use_grad_checkpointing, pretrain_zoo, pretrain_path):
+    vision_model = VisionTransformer(output_dim=project_embed_dim, **vision_kw)
+    text_model = TextTransformer(output_dim=project_embed_dim, **text_kw)
+    vision_model.set_grad_checkpointing(use_grad_checkpointing)
+    text_model.set_grad_checkpointing(use_grad_checkpointing)
+    model = CLIP(embed_dim=project_embed_dim, vision_model=vision_model, text_model=text_model,
+                 freeze_temperature=freeze_temperature)
+    if pretrain_zoo in ("openai", "open_clip") and pretrain_path is not None:
+        # a checkpoint already remapped to the flash + fast_conv1 naming (avion/models/utils.py:15-98)
+        sd = torch.load(pretrain_path, map_location="cpu")
+        sd = sd.get("state_dict", sd)
+        sd = {k[len("module."):] if k.startswith("module.") else k: v for k, v in sd.items()}
+        missing, unexpected = model.load_state_dict(sd, strict=False)
+        print("missing_keys: ", missing)
+        print("unexpected_keys: ", unexpected)
+    elif pretrain_zoo not in (None, "none", "random"):
+        raise NotImplementedError("no network on this box: pass pretrain_zoo='random' or a local pretrain_path")
+    return model
+
+
+def CLIP_VITB16(freeze_temperature=False, use_grad_checkpointing=False, use_bidirectional_lm=False, context_length=77,
+                patch_dropout=0.0, drop_path_rate=0.0, num_frames=1, use_fast_conv1=True, use_flash_attn=True,
+                project_embed_dim=512, pretrain_zoo="random", pretrain_path=None, **kwargs):
+    """avion/models/model_clip.py:102-177 (ViT-B/16 video tower + 12L/512 text tower)."""
+    return _build(dict(image_size=224, patch_size=16, width=768, layers=12, heads=12, mlp_ratio=4, patch_dropout=patch_dropout,
+                       drop_path_rate=drop_path_rate, num_frames=num_frames),
+                  dict(context_length=context_length, vocab_size=49408, width=512, heads=8, layers=12,
+                       causal_mask=not use_bidirectional_lm),
+                  project_embed_dim, freeze_temperature, use_grad_checkpointing, pretrain_zoo, pretrain_path)
+
+
+def CLIP_VITL14(*args, **kwargs):
+    """avion/models/model_clip.py:180-259.  Patch 14 needs a K=588 -> 640 padded patchify."""
+    raise NotImplementedError("ViT-L/14 is a later row of the scope table (patch 14 is not a multiple of 8)")

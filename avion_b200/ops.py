@@ -223,14 +223,14 @@ def head_fwd(x2d, row_idx, gamma, beta, proj, eps):
     return emb, (u, mean, rstd)
 
 
-def head_bwd(demb, x2d, row_idx, gamma, beta, proj, saved, dx2d, dgamma, dbeta, dproj):
+def head_bwd(demb, x2d, row_idx, gamma, beta, proj, saved, dx2d, dgamma, dbeta, dproj, normalized=True):
     u, mean, rstd = saved
     n = row_idx.numel()
     D, E = proj.shape
     ws = torch.empty(n, D + E, dtype=f32, device=x2d.device)
     _chk(demb, f32, "demb")
     _lib.call("avn_head_bwd", _p(demb), _p(x2d), _p(row_idx), _p(gamma), _p(beta), _p(proj), _p(u), _p(mean), _p(rstd), _p(dx2d),
-              _p(dgamma), _p(dbeta), _p(dproj), _p(ws), n, D, E, _stream(x2d))
+              _p(dgamma), _p(dbeta), _p(dproj), _p(ws), n, D, E, int(normalized), _stream(x2d))
 
 
 def infonce_fwd(img, txt, all_img, all_txt, scale, row_offset):

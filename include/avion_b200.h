@@ -118,7 +118,9 @@ int avn_head_fwd(const void* x, const int64_t* row_idx, const float* gamma, cons
 int avn_head_bwd(const float* demb, const void* x, const int64_t* row_idx, const float* gamma, const float* beta,
                  const float* proj,
                  const float* u, const float* mean, const float* rstd, void* dx, float* dgamma, float* dbeta,
-                 float* dproj, float* ws /* fp32 [n][D+E] workspace */, int n, int D, int E, avn_stream_t stream);
+                 float* dproj, float* ws /* fp32 [n][D+E] workspace */, int n, int D, int E,
+                 int normalized /* demb is the gradient of the normalised (1) or pre-normalise (0) output */,
+                 avn_stream_t stream);
 
 /* ---- L2: sharded InfoNCE (ClipLoss, avion/losses/losses.py:103-149, local rows x gathered columns) -------------
  * img,txt fp32 [n][E] local rows; all_img, all_txt fp32 [N][E] gathered; labels = row_offset + r.
