@@ -49,6 +49,11 @@ SIGNATURES = {
     "avn_infonce_bwd": [_vp, _vp, _vp, _vp, _f, _i, _i, _i, _i, _vp, _f, _vp, _vp, _vp, _vp],
 }
 
+# kernels launched per C-ABI call (for the bench's gpu_launches count); default 1
+KERNELS_PER_CALL = {"avn_attn_bwd": 3, "avn_infonce_bwd": 3, "avn_head_bwd": 2, "avn_pos_table_bwd": 2,
+                    "avn_token_embed_bwd": 2, "avn_sample_rrc_boxes": 0, "avn_device_check": 0, "avn_version": 0}
+launch_count = 0
+
 _lib = None
 
 
@@ -72,7 +77,9 @@ def load():
 
 
 def call(name, *args):
+    global launch_count
     lib = load()
+    launch_count += KERNELS_PER_CALL.get(name, 1)
     rc = getattr(lib, name)(*args)
     if rc != 0:
         raise RuntimeError(f"{name} failed ({rc}): {lib.avn_last_error().decode()}")

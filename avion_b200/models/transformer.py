@@ -125,7 +125,7 @@ class _VisionTowerFn(torch.autograd.Function):
         D = conv_w.shape[0]
         S = P + 1
         dev = patches.device
-        save = torch.is_grad_enabled() and any(t.requires_grad for t in (cls, conv_w, proj) + tuple(flat))
+        save = any(ctx.needs_input_grad)      # False under torch.no_grad() or with frozen parameters
         layers = E.cast_layers(_unflatten(flat))
         conv_bf = ops.cast_bf16(conv_w.detach())
         table = ops.pos_table_fwd(cls.detach(), pos.detach(), temporal.detach() if temporal is not None else None, T, G)
@@ -281,7 +281,7 @@ class _TextTowerFn(torch.autograd.Function):
         B, Lc = text.shape
         D = tok_emb.shape[1]
         dev = text.device
-        save = torch.is_grad_enabled() and any(t.requires_grad for t in (tok_emb, proj) + tuple(flat))
+        save = any(ctx.needs_input_grad)
         layers = E.cast_layers(_unflatten(flat))
         x0 = ops.token_embed_fwd(text.contiguous(), tok_emb.detach(), pos.detach())
         x, saved = E.blocks_forward(x0, layers, heads, eps, causal, ws, save)

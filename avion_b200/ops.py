@@ -13,6 +13,29 @@ from ._lib import (EPI_BIAS, EPI_BIAS_GELU, EPI_BIAS_GELU_DUAL, EPI_BIAS_RESIDUA
 bf16, f32 = torch.bfloat16, torch.float32
 _checked_devices = set()
 
+# Optional per-family device timing (bench.py): TIMED maps a family name to a list of (start, end) CUDA events recorded
+# on the launching stream around each call; None disables it.
+TIMED = None
+
+
+class _timed:
+    def __init__(self, name, t, work=0.0):
+        self.on = TIMED is not None
+        self.work = work
+        if self.on:
+            self.name = name
+            self.s, self.e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            self.stream = torch.cuda.current_stream(t.device)
+
+    def __enter__(self):
+        if self.on:
+            self.s.record(self.stream)
+
+    def __exit__(self, *a):
+        if self.on:
+            self.e.record(self.stream)
+            TIMED.setdefault(self.name, []).append((self.s, self.e, self.work))
+
 
 def _stream(t):
     dev = t.device
@@ -55,7 +78,9 @@ def clip_transform(frames_u8, crop, patch, mean, std, boxes=None, out=None):
         assert boxes.shape == (B, 3) and boxes.device == frames_u8.device
     m = (C.c_float * 3)(*[float(v) for v in mean])
     s = (C.c_float * 3)(*[float(v) for v in std])
-    _lib.call("avn_clip_transform_u8_bf16", _p(frames_u8), _p(out), B, T, Hs, Ws, crop, patch, _p(boxes), m, s, _stream(frames_u8))
+    with _timed("clip_transform", frames_u8, 3.0 * frames_u8.numel()):
+        _lib.call("avn_clip_transform_u8_bf16", _p(frames_u8), _p(out), B, T, Hs, Ws, crop, patch, _p(boxes), m, s,
+                  _stream(frames_u8))
     return out
 
 
@@ -68,7 +93,8 @@ def layernorm_fwd(x, gamma, beta, eps, out=None, save_stats=True):
     if save_stats:
         mean = torch.empty(rows, dtype=f32, device=x.device)
         rstd = torch.empty(rows, dtype=f32, device=x.device)
-    _lib.call("avn_layernorm_fwd", _p(x), _p(gamma), _p(beta), _p(y), _p(mean), _p(rstd), rows, D, float(eps), _stream(x))
+    with _timed("layernorm_fwd", x, 4.0 * rows * D):
+        _lib.call("avn_layernorm_fwd", _p(x), _p(gamma), _p(beta), _p(y), _p(mean), _p(rstd), rows, D, float(eps), _stream(x))
     return y, mean, rstd
 
 
@@ -77,8 +103,9 @@ def layernorm_bwd(dy, x, gamma, mean, rstd, dgamma, dbeta, dres=None, dcolsum=No
     D = x.shape[-1]
     rows = x.numel() // D
     dx = out if out is not None else torch.empty_like(x)
-    _lib.call("avn_layernorm_bwd", _p(dy), _p(x), _p(gamma), _p(mean), _p(rstd), _p(dres), _p(dx), _p(dgamma), _p(dbeta),
-              _p(dcolsum), rows, D, _stream(x))
+    with _timed("layernorm_bwd", x, (8.0 if dres is not None else 6.0) * rows * D):
+        _lib.call("avn_layernorm_bwd", _p(dy), _p(x), _p(gamma), _p(mean), _p(rstd), _p(dres), _p(dx), _p(dgamma), _p(dbeta),
+                  _p(dcolsum), rows, D, _stream(x))
     return dx
 
 
@@ -88,7 +115,8 @@ def gemm(mode, epi, M, N, K, A, lda, B, ldb, Cm, ldc, batch=1, a_bs=0, b_bs=0, c
     d = GemmDesc(mode, epi, M, N, K, batch, A.data_ptr(), lda, a_bs, B.data_ptr(), ldb, b_bs, Cm.data_ptr(), ldc, c_bs,
                  C2.data_ptr() if C2 is not None else None, bias.data_ptr() if bias is not None else None,
                  R.data_ptr() if R is not None else None, ldr, r_bs, splits)
-    _lib.call("avn_gemm_bf16", C.byref(d), _stream(A))
+    with _timed("gemm_%s" % ("nt", "nn", "tn")[mode], A, 2.0 * M * N * K * batch):
+        _lib.call("avn_gemm_bf16", C.byref(d), _stream(A))
 
 
 def linear_fwd(x, w, bias=None, epi=EPI_NONE, residual=None, out=None, out2=None):
@@ -137,7 +165,8 @@ def attn_fwd(qkv, heads, scale, causal=False, out=None):
     assert W3 == 3 * heads * 64, "head dim must be 64"
     o = out if out is not None else torch.empty(B, S, heads * 64, dtype=bf16, device=qkv.device)
     lse = torch.empty(B, heads, S, dtype=f32, device=qkv.device)
-    _lib.call("avn_attn_fwd", _p(qkv), _p(o), _p(lse), B, S, heads, float(scale), int(causal), _stream(qkv))
+    with _timed("attn_fwd", qkv, (2.0 if causal else 4.0) * B * heads * S * S * 64):
+        _lib.call("avn_attn_fwd", _p(qkv), _p(o), _p(lse), B, S, heads, float(scale), int(causal), _stream(qkv))
     return o, lse
 
 
@@ -149,8 +178,9 @@ def attn_bwd(qkv, o, do, lse, heads, scale, causal=False, dqkv=None, dq_acc=None
     delta = torch.empty(B, heads, S, dtype=f32, device=qkv.device)
     if dq_acc is None:
         dq_acc = torch.empty(B, S, heads * 64, dtype=f32, device=qkv.device)
-    _lib.call("avn_attn_bwd", _p(qkv), _p(o), _p(do), _p(lse), _p(dqkv), _p(delta), _p(dq_acc), B, S, heads, float(scale),
-              int(causal), _stream(qkv))
+    with _timed("attn_bwd", qkv, (5.0 if causal else 10.0) * B * heads * S * S * 64):
+        _lib.call("avn_attn_bwd", _p(qkv), _p(o), _p(do), _p(lse), _p(dqkv), _p(delta), _p(dq_acc), B, S, heads, float(scale),
+                  int(causal), _stream(qkv))
     return dqkv
 
 
@@ -173,7 +203,8 @@ def colsum(x, out):
     """out[N] (fp32) += column sums of x bf16 [rows,N]."""
     _chk(x, bf16, "x"); _chk(out, f32, "out")
     N = x.shape[-1]
-    _lib.call("avn_colsum_bf16", _p(x), N, _p(out), x.numel() // N, N, _stream(x))
+    with _timed("colsum", x, 2.0 * x.numel()):
+        _lib.call("avn_colsum_bf16", _p(x), N, _p(out), x.numel() // N, N, _stream(x))
     return out
 
 
