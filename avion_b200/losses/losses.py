@@ -6,6 +6,7 @@ import torch.distributed as dist
 import torch.nn as nn
 
 from .. import ops
+from . import _dist
 
 
 class _InfoNCEFn(torch.autograd.Function):
@@ -14,10 +15,7 @@ class _InfoNCEFn(torch.autograd.Function):
         img32, txt32 = img.detach().float().contiguous(), txt.detach().float().contiguous()
         n, E = img32.shape
         if world > 1:
-            packed = torch.stack([img32, txt32])                               # [2,n,E]
-            gathered = torch.empty(world, 2, n, E, dtype=torch.float32, device=img.device)
-            dist.all_gather_into_tensor(gathered, packed, group=group)        # ONE collective for both towers
-            both = gathered.permute(1, 0, 2, 3).reshape(2, world * n, E).contiguous()
+            both = _dist.gather_packed(img32, txt32, world, group)           # ONE collective for both towers
             all_img, all_txt = both[0], both[1]
         else:
             all_img, all_txt = img32, txt32
@@ -28,8 +26,7 @@ class _InfoNCEFn(torch.autograd.Function):
         if world > 1 and not local_loss:
             # the reference's default mode evaluates the full NxN problem on every rank (:119-123); its scalar is the
             # mean over all N rows = the mean of the rank-local means
-            dist.all_reduce(stats, op=dist.ReduceOp.SUM, group=group)
-            stats = stats / world
+            stats = _dist.mean_over_ranks(stats, world, group)
         ctx.save_for_backward(img32, txt32, all_img, all_txt, lse)
         ctx.cfg = (s, off, rank, world, local_loss, gather_with_grad, group, img.dtype, txt.dtype)
         loss, acc = stats[0].clone(), stats[1].clone()
@@ -44,9 +41,7 @@ class _InfoNCEFn(torch.autograd.Function):
         d_all, dscale = ops.infonce_bwd(img32, txt32, all_img, all_txt, s, off, lse, 1.0)
         if world > 1 and (gather_with_grad or not local_loss):
             # d_all holds this rank's contribution to every rank's features: sum them where they belong
-            inp = d_all.view(2, world, n, E).permute(1, 0, 2, 3).contiguous()  # [W,2,n,E]
-            local = torch.empty(2, n, E, dtype=torch.float32, device=img32.device)
-            dist.reduce_scatter_tensor(local, inp, op=dist.ReduceOp.SUM, group=group)
+            local = _dist.scatter_sum(d_all, world, group)
             if not gather_with_grad:
                 local = local / world       # full-matrix loss with constant remote features (:62-72) == 1/W of the sum
         else:

@@ -1,0 +1,62 @@
+"""world_size-2 gloo test (CPU) of the sharded-loss plumbing: packed all-gather layout, reduce-scatter of the feature
+gradients and the scalar all-reduce reproduce the reference's single-process ClipLoss on the concatenated batch
+(avion/losses/losses.py:119-123) - loss, accuracy and gradients.  The per-rank arithmetic is the oracle's here; on the
+GPU box tests/test_dist_gpu.py runs the same check through the CUDA kernels over NCCL."""
+import os
+import sys
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _worker(rank, world, port, n, E, q):
+    sys.path.insert(0, ROOT)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from avion_b200.losses import _dist
+        from oracle import clip_oracle as O
+        torch.manual_seed(0)
+        N = world * n
+        g_img = torch.nn.functional.normalize(torch.randn(N, E), dim=-1)
+        g_txt = torch.nn.functional.normalize(g_img + 0.5 * torch.randn(N, E), dim=-1)
+        scale = torch.tensor(9.0)
+        off = rank * n
+        both = _dist.gather_packed(g_img[off:off + n].contiguous(), g_txt[off:off + n].contiguous(), world)
+        assert torch.equal(both[0], g_img) and torch.equal(both[1], g_txt)
+        # rank-local rows against all columns; local features are rows off.. of the gathered tensors
+        ai, at = both[0].clone().requires_grad_(True), both[1].clone().requires_grad_(True)
+        out = O.clip_loss_local(ai[off:off + n], at[off:off + n], ai, at, scale, rank)
+        out["loss"].backward()
+        local = _dist.scatter_sum(torch.stack([ai.grad, at.grad]), world)
+        stats = _dist.mean_over_ranks(torch.stack([out["loss"].detach(), out["clip_acc"].float()]), world)
+        # single-process reference on the concatenated batch
+        fi, ft = g_img.clone().requires_grad_(True), g_txt.clone().requires_grad_(True)
+        full = O.clip_loss(fi, ft, scale)
+        full["loss"].backward()
+        ok = (torch.allclose(stats[0], full["loss"].detach(), atol=1e-6) and torch.allclose(stats[1], full["clip_acc"].float(), atol=1e-4)
+              and torch.allclose(local[0], world * fi.grad[off:off + n], atol=1e-6)
+              and torch.allclose(local[1], world * ft.grad[off:off + n], atol=1e-6))
+        q.put((rank, bool(ok)))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("n,E", [(4, 16), (7, 32)])
+def test_sharded_loss_plumbing_gloo_world2(n, E):
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29600 + (os.getpid() % 200) + n
+    procs = [ctx.Process(target=_worker, args=(r, world, port, n, E, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    res = dict(q.get(timeout=5) for _ in range(world))
+    assert res == {0: True, 1: True}
