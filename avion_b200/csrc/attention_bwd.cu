@@ -155,6 +155,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
             const float dlt = row_ok ? delta[stat_base + qrow] : 0.f;
             // valid columns of this thread's row: [0, limit) in tile coordinates
             const int limit = row_ok ? (causal ? min(S - kv0, qrow - kv0 + 1) : (S - kv0)) : 0;
+            const bool need_mask = (kv0 + TILE > S) || (q0 + TILE > S) || (causal && kv0 + TILE - 1 > q0);   // warp-uniform
             mbar_wait(&bars->sdp_full, t & 1);
             tc_fence_after();
             uint32_t pk[32], dsk[32];     // packed bf16: 64 P values and 64 dS values of this thread
@@ -165,17 +166,22 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
                 tmem_ld32(tmem_base + lane_addr + TM_DP + half * 64 + c * 32, dv);
                 tmem_ld_wait();
                 if (c == 1) { tc_fence_before(); mbar_arrive(&bars->sdp_free); }
+                const float2 sc2 = make_float2(scale_log2, scale_log2), nl2 = make_float2(-lse_l2, -lse_l2);
+                const float2 nd2 = make_float2(-dlt, -dlt), s2 = make_float2(scale, scale);
 #pragma unroll
                 for (int i = 0; i < 32; i += 2) {
-                    float p0 = exp2f(fmaf(__uint_as_float(sv[i]), scale_log2, -lse_l2));
-                    float p1 = exp2f(fmaf(__uint_as_float(sv[i + 1]), scale_log2, -lse_l2));
-                    const int col = half * 64 + c * 32 + i;
-                    if (col >= limit) p0 = 0.f;
-                    if (col + 1 >= limit) p1 = 0.f;
-                    const float d0 = p0 * (__uint_as_float(dv[i]) - dlt) * scale;
-                    const float d1 = p1 * (__uint_as_float(dv[i + 1]) - dlt) * scale;
-                    pk[c * 16 + (i >> 1)] = pack_bf16(p0, p1);
-                    dsk[c * 16 + (i >> 1)] = pack_bf16(d0, d1);
+                    const float2 x = __ffma2_rn(make_float2(__uint_as_float(sv[i]), __uint_as_float(sv[i + 1])), sc2, nl2);
+                    float2 p = make_float2(ex2(x.x), ex2(x.y));
+                    if (need_mask) {
+                        const int col = half * 64 + c * 32 + i;
+                        if (col >= limit) p.x = 0.f;
+                        if (col + 1 >= limit) p.y = 0.f;
+                    }
+                    // dS = scale * P o (dP - delta)
+                    const float2 t = __fmul2_rn(__fadd2_rn(make_float2(__uint_as_float(dv[i]), __uint_as_float(dv[i + 1])), nd2), s2);
+                    const float2 d = __fmul2_rn(p, t);
+                    pk[c * 16 + (i >> 1)] = pack_bf16(p.x, p.y);
+                    dsk[c * 16 + (i >> 1)] = pack_bf16(d.x, d.y);
                 }
             }
             // previous tile's MMAs must be done before P/dS smem is overwritten; drain its dQ on the way

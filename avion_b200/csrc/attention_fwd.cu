@@ -133,10 +133,11 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
             const uint32_t t_s = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + TM_S + w * TILE;
             const uint32_t t_o = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + TM_O + w * HD;
             uint8_t* sP = smem + OFF_P + w * P_BYTES;
-            float o[HD];
+            float2 o2[HD / 2];                       // O accumulator, kept one rescale behind (relative to the previous maximum)
 #pragma unroll
-            for (int i = 0; i < HD; ++i) o[i] = 0.f;
-            float m = -INFINITY, l = 0.f;
+            for (int i = 0; i < HD / 2; ++i) o2[i] = make_float2(0.f, 0.f);
+            float m = -INFINITY, l = 0.f, alpha_prev = 1.f;
+            const float2 sc2 = make_float2(scale_log2, scale_log2);
             for (int j = 0; j < n_my; ++j) {
                 const int kv0 = j * TILE;
                 const bool need_mask = (kv0 + TILE > S) || (causal && kv0 + TILE - 1 > q0);
@@ -159,49 +160,55 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
                     }
                 }
                 const float m_new = fmaxf(m, mx * scale_log2);
-                const float alpha = exp2f(m - m_new);
-                // fold the previous tile's P*V into the register accumulator, then rescale to the new maximum
+                const float alpha = ex2(m - m_new);
+                // fold the previous tile's P*V into the register accumulator: o = o * alpha_prev + PV_{j-1}
                 // (waiting for P*V of tile j-1 here also guarantees that the MMA has finished READING this group's P
                 //  buffer, which pass 2 is about to overwrite)
                 if (j > 0) {
                     mbar_wait(&bars->o_full[w], (j - 1) & 1);
                     tc_fence_after();
+                    const float2 a2 = make_float2(alpha_prev, alpha_prev);
 #pragma unroll
                     for (int c = 0; c < 2; ++c) {
                         uint32_t v[32];
                         tmem_ld32(t_o + c * 32, v);
                         tmem_ld_wait();
 #pragma unroll
-                        for (int i = 0; i < 32; ++i) o[c * 32 + i] = (o[c * 32 + i] + __uint_as_float(v[i])) * alpha;
+                        for (int i = 0; i < 16; ++i)
+                            o2[c * 16 + i] = __ffma2_rn(o2[c * 16 + i], a2, make_float2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1])));
                     }
                     tc_fence_before();
                 }
+                alpha_prev = alpha;
                 // pass 2: probabilities -> bf16 -> smem (two K-major 128B-swizzled [128][64] sub-tiles)
-                float rs = 0.f;
+                const float2 nm2 = make_float2(-m_new, -m_new);
+                float2 rs2 = make_float2(0.f, 0.f);
 #pragma unroll
                 for (int c = 0; c < 4; ++c) {
                     uint32_t v[32];
                     tmem_ld32(t_s + c * 32, v);
                     tmem_ld_wait();
                     if (c == 3) { tc_fence_before(); mbar_arrive(&bars->s_free[w]); }
-                    float p[32];
+                    uint32_t pk[16];
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) {
-                        float e = exp2f(fmaf(__uint_as_float(v[i]), scale_log2, -m_new));
-                        if (need_mask && c * 32 + i >= limit) e = 0.f;
-                        p[i] = e;
-                        rs += e;
+                    for (int i = 0; i < 16; ++i) {
+                        const float2 x = __ffma2_rn(make_float2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1])), sc2, nm2);
+                        float2 e = make_float2(ex2(x.x), ex2(x.y));
+                        if (need_mask) {
+                            if (c * 32 + 2 * i >= limit) e.x = 0.f;
+                            if (c * 32 + 2 * i + 1 >= limit) e.y = 0.f;
+                        }
+                        rs2 = __fadd2_rn(rs2, e);
+                        pk[i] = pack_bf16(e.x, e.y);
                     }
                     uint8_t* sub = sP + (c >> 1) * (P_BYTES / 2) + row * 128;
 #pragma unroll
                     for (int i = 0; i < 4; ++i) {
                         const int c16 = (c & 1) * 4 + i;
-                        *(uint4*)(sub + ((c16 ^ (row & 7)) << 4)) =
-                            make_uint4(pack_bf16(p[8 * i], p[8 * i + 1]), pack_bf16(p[8 * i + 2], p[8 * i + 3]),
-                                       pack_bf16(p[8 * i + 4], p[8 * i + 5]), pack_bf16(p[8 * i + 6], p[8 * i + 7]));
+                        *(uint4*)(sub + ((c16 ^ (row & 7)) << 4)) = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
                     }
                 }
-                l = fmaf(l, alpha, rs);
+                l = fmaf(l, alpha, rs2.x + rs2.y);
                 m = m_new;
                 fence_proxy_async_smem();
                 mbar_arrive(&bars->p_ready[w]);
@@ -210,13 +217,20 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
             mbar_wait(&bars->o_full[w], (n_my - 1) & 1);
             tc_fence_after();
             const float inv_l = 1.f / l;
+            float o[HD];
+            {
+                const float2 a2 = make_float2(alpha_prev, alpha_prev), il2 = make_float2(inv_l, inv_l);
 #pragma unroll
-            for (int c = 0; c < 2; ++c) {
-                uint32_t v[32];
-                tmem_ld32(t_o + c * 32, v);
-                tmem_ld_wait();
+                for (int c = 0; c < 2; ++c) {
+                    uint32_t v[32];
+                    tmem_ld32(t_o + c * 32, v);
+                    tmem_ld_wait();
 #pragma unroll
-                for (int i = 0; i < 32; ++i) o[c * 32 + i] = (o[c * 32 + i] + __uint_as_float(v[i])) * inv_l;
+                    for (int i = 0; i < 16; ++i) {
+                        const float2 r = __fmul2_rn(__ffma2_rn(o2[c * 16 + i], a2, make_float2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]))), il2);
+                        o[c * 32 + 2 * i] = r.x; o[c * 32 + 2 * i + 1] = r.y;
+                    }
+                }
             }
             if (qrow < S) lse[((long long)b * H + h) * S + qrow] = (m + log2f(l)) * 0.6931471805599453f;
             // O tile -> swizzled smem (reuses this group's P buffer: its last MMA has completed) -> TMA store

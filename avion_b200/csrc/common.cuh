@@ -185,6 +185,13 @@ __device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t* r) {
 }
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
+// ---- fast exp2 / packed fp32x2 (Blackwell FFMA2/FADD2/FMUL2: two fp32 lanes per issue slot) ----------------------------
+__device__ __forceinline__ float ex2(float x) {      // one MUFU.EX2, no range fix-up (inputs here are <= 0)
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
 // ---- small math -----------------------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
     __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
@@ -193,22 +200,34 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
 __device__ __forceinline__ float2 unpack_bf16(uint32_t u) {
     return __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&u));
 }
-// erf by Abramowitz-Stegun 7.1.26 (|abs err| < 1.5e-7, far below bf16 resolution); returns erf(x/sqrt2) and exp(-x^2/2).
-__device__ __forceinline__ float erf_half_arg(float x, float& e) {
-    float z = fabsf(x) * 0.70710678118654752f;
-    float t = __frcp_rn(fmaf(0.3275911f, z, 1.0f));
-    e = __expf(-z * z);
-    float poly = fmaf(fmaf(fmaf(fmaf(1.061405429f, t, -1.453152027f), t, 1.421413741f), t, -0.284496736f), t, 0.254829592f) * t;
-    float r = fmaf(-poly, e, 1.0f);
-    return copysignf(r, x);
+__device__ __forceinline__ float rcp_approx(float x) {
+    float y;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+// GELU with the exact-erf definition (nn.GELU() default), erf by Abramowitz-Stegun 7.1.26 (|abs err| < 1.5e-7 on erf, far
+// below bf16 resolution).  With z = |x|/sqrt2, t = 1/(1 + p z), e = exp(-z^2):
+//   q(x) = 0.5 * poly(t) * e = 1 - Phi(|x|),   gelu(x) = relu(x) - |x| q,   gelu'(x) = Phi(x) + x * e / sqrt(2 pi).
+// Two MUFU (rcp, ex2) + ~10 FMA-pipe instructions per element.
+__device__ __forceinline__ float gelu_tail(float x, float& e) {
+    const float ax = fabsf(x);
+    const float t = rcp_approx(fmaf(0.3275911f * 0.70710678118654752f, ax, 1.0f));
+    e = ex2(x * x * -0.72134752044448170f);                     // exp(-x^2/2)
+    float p = fmaf(0.5f * 1.061405429f, t, 0.5f * -1.453152027f);
+    p = fmaf(p, t, 0.5f * 1.421413741f);
+    p = fmaf(p, t, 0.5f * -0.284496736f);
+    p = fmaf(p, t, 0.5f * 0.254829592f);
+    return p * t * e;
 }
 __device__ __forceinline__ float gelu_erf(float x) {
     float e;
-    return 0.5f * x * (1.0f + erf_half_arg(x, e));
+    const float q = gelu_tail(x, e);
+    return fmaf(-fabsf(x), q, fmaxf(x, 0.f));
 }
 __device__ __forceinline__ float gelu_erf_grad(float x) {
     float e;
-    float cdf = 0.5f * (1.0f + erf_half_arg(x, e));
+    const float q = gelu_tail(x, e);
+    const float cdf = x >= 0.f ? 1.0f - q : q;
     return fmaf(x * 0.3989422804014327f, e, cdf);
 }
 

@@ -64,7 +64,7 @@ ln_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ gam
 }
 
 template <int VPL>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 2)
 ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma,
               const float* __restrict__ mean_in, const float* __restrict__ rstd_in, const __nv_bfloat16* __restrict__ dres,
               __nv_bfloat16* __restrict__ dx, float* __restrict__ dgamma, float* __restrict__ dbeta, float* __restrict__ dcolsum,
@@ -72,64 +72,72 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restr
     extern __shared__ float red[];       // [8 warps][3][VPL*256]
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int nvec = D >> 3;
-    float ag[VPL][8], ab[VPL][8], ac[VPL][8], g[VPL][8];
+    // per-lane column accumulators (dgamma, dbeta, column sum of dx); x / dy stay packed (bf16x2) to keep the register
+    // count low enough for two CTAs per SM - this kernel lives on memory-level parallelism
+    float ag[VPL][8], ab[VPL][8], ac[VPL][8];
 #pragma unroll
-    for (int j = 0; j < VPL; ++j) {
-        const int i = lane + 32 * j;
+    for (int j = 0; j < VPL; ++j)
 #pragma unroll
-        for (int e = 0; e < 8; ++e) { ag[j][e] = ab[j][e] = ac[j][e] = 0.f; g[j][e] = (i < nvec) ? __ldg(gamma + i * 8 + e) : 0.f; }
-    }
+        for (int e = 0; e < 8; ++e) ag[j][e] = ab[j][e] = ac[j][e] = 0.f;
     for (long long row = (long long)blockIdx.x * 8 + warp; row < rows; row += (long long)gridDim.x * 8) {
-        const float mean = mean_in[row], rstd = rstd_in[row];
+        const float mean = __ldg(mean_in + row), rstd = __ldg(rstd_in + row);
         const uint4* xr = (const uint4*)(x + row * D);
         const uint4* dyr = (const uint4*)(dy + row * D);
-        float xh[VPL][8], gy[VPL][8];
+        const uint4* drr = dres ? (const uint4*)(dres + row * D) : nullptr;
+        uint4 ux[VPL], ud[VPL], ur[VPL];
+#pragma unroll
+        for (int j = 0; j < VPL; ++j) {
+            const int i = lane + 32 * j;
+            ux[j] = ud[j] = ur[j] = make_uint4(0, 0, 0, 0);
+            if (i < nvec) {
+                ux[j] = __ldg(xr + i);
+                ud[j] = __ldg(dyr + i);
+                if (drr) ur[j] = __ldg(drr + i);
+            }
+        }
         float s1 = 0.f, s2 = 0.f;
 #pragma unroll
         for (int j = 0; j < VPL; ++j) {
             const int i = lane + 32 * j;
             if (i < nvec) {
-                const uint4 ux = __ldg(xr + i), ud = __ldg(dyr + i);
-                const uint32_t wx[4] = {ux.x, ux.y, ux.z, ux.w}, wd[4] = {ud.x, ud.y, ud.z, ud.w};
+                const uint32_t wx[4] = {ux[j].x, ux[j].y, ux[j].z, ux[j].w}, wd[4] = {ud[j].x, ud[j].y, ud[j].z, ud[j].w};
+                const float4 g0 = __ldg((const float4*)(gamma + i * 8)), g1 = __ldg((const float4*)(gamma + i * 8 + 4));
+                const float g[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
                     const float2 fx = unpack_bf16(wx[e]), fd = unpack_bf16(wd[e]);
                     const float h0 = (fx.x - mean) * rstd, h1 = (fx.y - mean) * rstd;
-                    xh[j][2 * e] = h0; xh[j][2 * e + 1] = h1;
-                    ag[j][2 * e] += fd.x * h0; ag[j][2 * e + 1] += fd.y * h1;
+                    ag[j][2 * e] = fmaf(fd.x, h0, ag[j][2 * e]); ag[j][2 * e + 1] = fmaf(fd.y, h1, ag[j][2 * e + 1]);
                     ab[j][2 * e] += fd.x; ab[j][2 * e + 1] += fd.y;
-                    const float t0 = fd.x * g[j][2 * e], t1 = fd.y * g[j][2 * e + 1];
-                    gy[j][2 * e] = t0; gy[j][2 * e + 1] = t1;
-                    s1 += t0 + t1; s2 += t0 * h0 + t1 * h1;
+                    const float t0 = fd.x * g[2 * e], t1 = fd.y * g[2 * e + 1];
+                    s1 += t0 + t1; s2 = fmaf(t0, h0, fmaf(t1, h1, s2));
                 }
-            } else {
-#pragma unroll
-                for (int e = 0; e < 8; ++e) { xh[j][e] = 0.f; gy[j][e] = 0.f; }
             }
         }
         const float c1 = warp_sum(s1) / D, c2 = warp_sum(s2) / D;
         uint4* dxr = (uint4*)(dx + row * D);
-        const uint4* drr = dres ? (const uint4*)(dres + row * D) : nullptr;
 #pragma unroll
         for (int j = 0; j < VPL; ++j) {
             const int i = lane + 32 * j;
             if (i < nvec) {
-                float o[8];
+                const uint32_t wx[4] = {ux[j].x, ux[j].y, ux[j].z, ux[j].w}, wd[4] = {ud[j].x, ud[j].y, ud[j].z, ud[j].w};
+                const uint32_t wr[4] = {ur[j].x, ur[j].y, ur[j].z, ur[j].w};
+                const float4 g0 = __ldg((const float4*)(gamma + i * 8)), g1 = __ldg((const float4*)(gamma + i * 8 + 4));
+                const float g[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+                uint32_t po[4];
 #pragma unroll
-                for (int e = 0; e < 8; ++e) o[e] = rstd * (gy[j][e] - c1 - xh[j][e] * c2);
-                if (drr) {
-                    const uint4 ur = __ldg(drr + i);
-                    const uint32_t wr[4] = {ur.x, ur.y, ur.z, ur.w};
-#pragma unroll
-                    for (int e = 0; e < 4; ++e) { const float2 f = unpack_bf16(wr[e]); o[2 * e] += f.x; o[2 * e + 1] += f.y; }
+                for (int e = 0; e < 4; ++e) {
+                    const float2 fx = unpack_bf16(wx[e]), fd = unpack_bf16(wd[e]), fr = unpack_bf16(wr[e]);
+                    const float h0 = (fx.x - mean) * rstd, h1 = (fx.y - mean) * rstd;
+                    const float o0 = fmaf(rstd, fd.x * g[2 * e] - c1 - h0 * c2, fr.x);
+                    const float o1 = fmaf(rstd, fd.y * g[2 * e + 1] - c1 - h1 * c2, fr.y);
+                    po[e] = pack_bf16(o0, o1);
+                    if (dcolsum) {   // column sum of the values actually stored (bf16-rounded), as the next consumer sees them
+                        const float2 f = unpack_bf16(po[e]);
+                        ac[j][2 * e] += f.x; ac[j][2 * e + 1] += f.y;
+                    }
                 }
-                const uint4 packed = make_uint4(pack_bf16(o[0], o[1]), pack_bf16(o[2], o[3]), pack_bf16(o[4], o[5]), pack_bf16(o[6], o[7]));
-                dxr[i] = packed;
-                if (dcolsum) {       // column sum of the values actually stored (bf16-rounded), as the next consumer sees them
-                    const uint32_t wp[4] = {packed.x, packed.y, packed.z, packed.w};
-#pragma unroll
-                    for (int e = 0; e < 4; ++e) { const float2 f = unpack_bf16(wp[e]); ac[j][2 * e] += f.x; ac[j][2 * e + 1] += f.y; }
-                }
+                dxr[i] = make_uint4(po[0], po[1], po[2], po[3]);
             }
         }
     }
@@ -162,7 +170,7 @@ int launch_bwd(const void* dy, const void* x, const float* gamma, const float* m
     auto kern = ln_bwd_kernel<VPL>;
     AVN_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     long long blocks = (rows + 7) / 8;
-    const long long cap = (long long)avn_num_sms() * 4;
+    const long long cap = (long long)avn_num_sms() * 2;      // two resident CTAs per SM, each warp loops over rows
     if (blocks > cap) blocks = cap;
     kern<<<(int)blocks, 256, smem, stream>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, gamma, mean, rstd,
                                              (const __nv_bfloat16*)dres, (__nv_bfloat16*)dx, dgamma, dbeta, dcolsum, rows, D);
