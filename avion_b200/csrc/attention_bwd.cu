@@ -15,22 +15,44 @@ namespace {
 using namespace avn;
 
 constexpr int TILE = 128, HD = 64;
-constexpr int NTHREADS = 320;
+constexpr int NTHREADS = 384;     // warps 0-7 math, 8 MMA issuer, 9 TMA producer, 10-11 idle (complete the warpgroup)
 constexpr int T16 = TILE * HD * 2;                // 16 KB: one [128][64] bf16 tile
 constexpr int OFF_K = 0, OFF_V = T16;
 constexpr int OFF_Q = 2 * T16;                    // 2 stages
 constexpr int OFF_DO = 4 * T16;                   // 2 stages
-constexpr int OFF_P = 6 * T16;                    // 32 KB
-constexpr int OFF_DS = 8 * T16;                   // 32 KB
-constexpr int OFF_DQ = 10 * T16;                  // 2 x 16 KB fp32 staging ([128][32 fp32] per column half)
-constexpr int OFF_BAR = 12 * T16;
+constexpr int OFF_P = 6 * T16;                    // 2 buffers x 32 KB ([q][kv] bf16, two 64-column sub-tiles each)
+constexpr int OFF_DS = 10 * T16;                  // 2 buffers x 32 KB
+constexpr int OFF_BAR = 14 * T16;
 constexpr int SMEM_TOTAL = OFF_BAR + 256 + 1024;
 constexpr uint32_t TM_S = 0, TM_DP = 128, TM_DV = 256, TM_DK = 320, TM_DQ = 384;
+// The P buffer of tile t doubles as the fp32 staging tile of dQ_t once the MMAs of tile t have completed.
 
 struct Bars {
-    uint64_t kv_full, qdo_full[2], qdo_empty[2], sdp_full, sdp_free, pds_ready, dq_full;
+    uint64_t kv_full, qdo_full[2], qdo_empty[2], sdp_full, sdp_free, pds_ready, dq_full, dq_free;
     uint32_t tmem_ptr;
 };
+
+
+// One 32-column chunk of a row: P = exp2(S*scale_log2 - lse_l2), dS = scale * P o (dP - delta) -> packed bf16 pairs.
+template <bool MASK>
+__device__ __forceinline__ void pds_chunk(const uint32_t* sv, const uint32_t* dv, uint32_t* pk, uint32_t* dsk, float scale_log2,
+                                          float lse_l2, float dlt, float scale, int col0, int limit) {
+    const float2 sc2 = make_float2(scale_log2, scale_log2), nl2 = make_float2(-lse_l2, -lse_l2);
+    const float2 nd2 = make_float2(-dlt * scale, -dlt * scale), s2 = make_float2(scale, scale);
+#pragma unroll
+    for (int i = 0; i < 32; i += 2) {
+        const float2 x = __ffma2_rn(make_float2(__uint_as_float(sv[i]), __uint_as_float(sv[i + 1])), sc2, nl2);
+        float2 p = make_float2(ex2(x.x), ex2(x.y));
+        if (MASK) {
+            if (col0 + i >= limit) p.x = 0.f;
+            if (col0 + i + 1 >= limit) p.y = 0.f;
+        }
+        const float2 t = __ffma2_rn(make_float2(__uint_as_float(dv[i]), __uint_as_float(dv[i + 1])), s2, nd2);   // scale*(dP - delta)
+        const float2 d = __fmul2_rn(p, t);
+        pk[i >> 1] = pack_bf16(p.x, p.y);
+        dsk[i >> 1] = pack_bf16(d.x, d.y);
+    }
+}
 
 __global__ void __launch_bounds__(NTHREADS, 1)
 attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
@@ -51,7 +73,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
         mbar_init(&bars->kv_full, 1);
         for (int i = 0; i < 2; ++i) { mbar_init(&bars->qdo_full[i], 1); mbar_init(&bars->qdo_empty[i], 1); }
         mbar_init(&bars->sdp_full, 1); mbar_init(&bars->sdp_free, 256);
-        mbar_init(&bars->pds_ready, 256); mbar_init(&bars->dq_full, 1);
+        mbar_init(&bars->pds_ready, 256); mbar_init(&bars->dq_full, 1); mbar_init(&bars->dq_free, 256);
         fence_barrier_init();
     }
     if (warp == 8) tmem_alloc(&bars->tmem_ptr, 512);
@@ -60,8 +82,12 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
     tc_fence_after();
     const uint32_t tmem_base = bars->tmem_ptr;
 
-    if (warp == 9) {
+    // the 8 math warps take the registers of the control warpgroup (setmaxnreg is per warpgroup: warps 8-11 all shrink)
+    if (warp >= 10) {
+        reg_dec<40>();       // idle warps: only complete the third warpgroup
+    } else if (warp == 9) {
         // ===================== TMA producer =====================
+        reg_dec<40>();
         if (lane == 0) {
             mbar_expect_tx(&bars->kv_full, 2 * T16);
             tma_load_3d(smem + OFF_K, &tmQKV, &bars->kv_full, (H + h) * HD, kv0, b);
@@ -76,12 +102,12 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
         }
     } else if (warp == 8) {
         // ===================== MMA issuer =====================
+        reg_dec<40>();
         if (lane == 0 && n_i > 0) {
             constexpr uint32_t idesc_s = umma_idesc_bf16(TILE, TILE, false, false);
             constexpr uint32_t idesc_dkv = umma_idesc_bf16(TILE, HD, true, true);
             constexpr uint32_t idesc_dq = umma_idesc_bf16(TILE, HD, false, true);
             const uint32_t ka = smem_u32(smem + OFF_K), va = smem_u32(smem + OFF_V);
-            const uint32_t pa = smem_u32(smem + OFF_P), dsa = smem_u32(smem + OFF_DS);
             auto issue_sdp = [&](int t) {
                 const int st = t & 1;
                 mbar_wait(&bars->qdo_full[st], (t >> 1) & 1);
@@ -104,6 +130,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
                 mbar_wait(&bars->pds_ready, t & 1);
                 tc_fence_after();
                 const uint32_t qa = smem_u32(smem + OFF_Q + st * T16), doa = smem_u32(smem + OFF_DO + st * T16);
+                const uint32_t pa = smem_u32(smem + OFF_P + st * 2 * T16), dsa = smem_u32(smem + OFF_DS + st * 2 * T16);
 #pragma unroll
                 for (int k = 0; k < TILE / 16; ++k)      // dV += P^T dO   (A = P as MN-major, B = dO as MN-major)
                     umma_ss(tmem_base + TM_DV, umma_smem_desc(pa + k * 2048, 16384, 1024), umma_smem_desc(doa + k * 2048, 8192, 1024),
@@ -112,6 +139,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
                 for (int k = 0; k < TILE / 16; ++k)      // dK += dS^T Q
                     umma_ss(tmem_base + TM_DK, umma_smem_desc(dsa + k * 2048, 16384, 1024), umma_smem_desc(qa + k * 2048, 8192, 1024),
                             idesc_dkv, (t > 0 || k > 0) ? 1u : 0u);
+                if (t > 0) { mbar_wait(&bars->dq_free, (t - 1) & 1); tc_fence_after(); }   // dQ_{t-1} has left TMEM
 #pragma unroll
                 for (int k = 0; k < TILE / 16; ++k)      // dQ_i = dS K_j  (A = dS K-major, B = K_j as MN-major)
                     umma_ss(tmem_base + TM_DQ, umma_smem_desc(dsa + (k >> 2) * 16384 + (k & 3) * 32, 16, 1024),
@@ -120,25 +148,27 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
                 umma_commit(&bars->qdo_empty[st]);
             }
         }
-    } else if (n_i > 0) {
+    } else {
         // ===================== compute warps: thread = (row, column half) =====================
+        reg_inc<232>();
+        if (n_i > 0) {
         const int half = warp >> 2;
         const int row = (warp & 3) * 32 + lane;
         const uint32_t lane_addr = (uint32_t)((warp & 3) * 32) << 16;
         const float scale_log2 = scale * 1.4426950408889634f;
-        uint8_t* stg = smem + OFF_DQ + half * T16;
         const bool leader = (threadIdx.x & 127) == 0;
         const long long stat_base = ((long long)b * H + h) * S;
 
-        auto drain_dq = [&](int t) {       // partial dQ of query tile t: TMEM -> fp32 smem -> TMA reduce-add
-            mbar_wait(&bars->dq_full, t & 1);
+        // partial dQ of query tile t: TMEM -> fp32 staging (the P buffer of tile t, free now) -> TMA reduce-add
+        auto drain_dq = [&](int t) {
+            mbar_wait(&bars->dq_full, t & 1);      // all MMAs of tile t are complete
             tc_fence_after();
             uint32_t v[32];
             tmem_ld32(tmem_base + lane_addr + TM_DQ + half * 32, v);
             tmem_ld_wait();
             tc_fence_before();
-            if (leader) tma_wait_group_read0();
-            named_bar_sync(1 + half, 128);
+            mbar_arrive(&bars->dq_free);
+            uint8_t* stg = smem + OFF_P + (t & 1) * 2 * T16 + half * T16;
 #pragma unroll
             for (int i = 0; i < 8; ++i)
                 *(uint4*)(stg + row * 128 + ((i ^ (row & 7)) << 4)) = make_uint4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
@@ -147,12 +177,18 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
             if (leader) { tma_reduce_add_3d(&tmDQ, stg, h * HD + half * 32, (i0 + t) * TILE, b); tma_commit_group(); }
         };
 
+        float lse_nx = 0.f, dlt_nx = 0.f;
+        { const int qr = i0 * TILE + row; if (qr < S) { lse_nx = __ldg(lse + stat_base + qr); dlt_nx = __ldg(delta + stat_base + qr); } }
         for (int t = 0; t < n_i; ++t) {
             const int q0 = (i0 + t) * TILE;
             const int qrow = q0 + row;
             const bool row_ok = qrow < S;
-            const float lse_l2 = row_ok ? lse[stat_base + qrow] * 1.4426950408889634f : 0.f;
-            const float dlt = row_ok ? delta[stat_base + qrow] : 0.f;
+            const float lse_l2 = lse_nx * 1.4426950408889634f, dlt = dlt_nx;
+            if (t + 1 < n_i) {                      // prefetch the next tile's row statistics
+                const int qr = qrow + TILE;
+                lse_nx = 0.f; dlt_nx = 0.f;
+                if (qr < S) { lse_nx = __ldg(lse + stat_base + qr); dlt_nx = __ldg(delta + stat_base + qr); }
+            }
             // valid columns of this thread's row: [0, limit) in tile coordinates
             const int limit = row_ok ? (causal ? min(S - kv0, qrow - kv0 + 1) : (S - kv0)) : 0;
             const bool need_mask = (kv0 + TILE > S) || (q0 + TILE > S) || (causal && kv0 + TILE - 1 > q0);   // warp-uniform
@@ -166,29 +202,17 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
                 tmem_ld32(tmem_base + lane_addr + TM_DP + half * 64 + c * 32, dv);
                 tmem_ld_wait();
                 if (c == 1) { tc_fence_before(); mbar_arrive(&bars->sdp_free); }
-                const float2 sc2 = make_float2(scale_log2, scale_log2), nl2 = make_float2(-lse_l2, -lse_l2);
-                const float2 nd2 = make_float2(-dlt, -dlt), s2 = make_float2(scale, scale);
-#pragma unroll
-                for (int i = 0; i < 32; i += 2) {
-                    const float2 x = __ffma2_rn(make_float2(__uint_as_float(sv[i]), __uint_as_float(sv[i + 1])), sc2, nl2);
-                    float2 p = make_float2(ex2(x.x), ex2(x.y));
-                    if (need_mask) {
-                        const int col = half * 64 + c * 32 + i;
-                        if (col >= limit) p.x = 0.f;
-                        if (col + 1 >= limit) p.y = 0.f;
-                    }
-                    // dS = scale * P o (dP - delta)
-                    const float2 t = __fmul2_rn(__fadd2_rn(make_float2(__uint_as_float(dv[i]), __uint_as_float(dv[i + 1])), nd2), s2);
-                    const float2 d = __fmul2_rn(p, t);
-                    pk[c * 16 + (i >> 1)] = pack_bf16(p.x, p.y);
-                    dsk[c * 16 + (i >> 1)] = pack_bf16(d.x, d.y);
-                }
+                if (need_mask) pds_chunk<true>(sv, dv, pk + c * 16, dsk + c * 16, scale_log2, lse_l2, dlt, scale, half * 64 + c * 32, limit);
+                else pds_chunk<false>(sv, dv, pk + c * 16, dsk + c * 16, scale_log2, lse_l2, dlt, scale, half * 64 + c * 32, limit);
             }
-            // previous tile's MMAs must be done before P/dS smem is overwritten; drain its dQ on the way
-            if (t > 0) drain_dq(t - 1);
-            // this thread's 64 columns = sub-tile `half`, all 8 16-byte chunks of its row
-            uint8_t* prow = smem + OFF_P + half * 16384 + row * 128;
-            uint8_t* drow = smem + OFF_DS + half * 16384 + row * 128;
+            // buffer t&1 last held P/dS of tile t-2 (its MMAs completed before drain_dq(t-2) returned) and, in its P half,
+            // the staging tile of dQ_{t-2}: the TMA reduce must have finished reading it
+            if (t >= 2) {
+                if (leader) tma_wait_group_read0();
+                named_bar_sync(1 + half, 128);
+            }
+            uint8_t* prow = smem + OFF_P + (t & 1) * 2 * T16 + half * T16 + row * 128;
+            uint8_t* drow = smem + OFF_DS + (t & 1) * 2 * T16 + half * T16 + row * 128;
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
                 const int off = (i ^ (row & 7)) << 4;
@@ -197,17 +221,18 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
             }
             fence_proxy_async_smem();
             mbar_arrive(&bars->pds_ready);
+            if (t > 0) drain_dq(t - 1);            // overlaps the MMAs of tile t
         }
         drain_dq(n_i - 1);      // also guarantees that dV and dK are complete
-        // dV, dK: TMEM -> bf16 -> swizzled smem (P / dS buffers are free now) -> TMA store into dqkv
+        // dV, dK: TMEM -> bf16 -> swizzled smem (the dS buffers are free now and never touched by the dQ reduces) -> TMA store
         {
             uint32_t v[32], k[32];
             tmem_ld32(tmem_base + lane_addr + TM_DV + half * 32, v);
             tmem_ld32(tmem_base + lane_addr + TM_DK + half * 32, k);
             tmem_ld_wait();
             tc_fence_before();
-            uint8_t* vrow = smem + OFF_P + row * 128;
-            uint8_t* krow = smem + OFF_DS + row * 128;
+            uint8_t* vrow = smem + OFF_DS + row * 128;
+            uint8_t* krow = smem + OFF_DS + 2 * T16 + row * 128;
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
                 const int off = ((half * 4 + i) ^ (row & 7)) << 4;
@@ -223,12 +248,13 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
             fence_proxy_async_smem();
             named_bar_sync(3, 256);
             if (threadIdx.x == 0) {
-                tma_store_3d(&tmDQKV, smem + OFF_DS, (H + h) * HD, kv0, b);
-                tma_store_3d(&tmDQKV, smem + OFF_P, (2 * H + h) * HD, kv0, b);
+                tma_store_3d(&tmDQKV, smem + OFF_DS + 2 * T16, (H + h) * HD, kv0, b);
+                tma_store_3d(&tmDQKV, smem + OFF_DS, (2 * H + h) * HD, kv0, b);
                 tma_commit_group();
             }
             if (leader) tma_wait_group0();
         }
+        }   // n_i > 0
     }
     tc_fence_before();
     __syncthreads();

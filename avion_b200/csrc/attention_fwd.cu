@@ -3,8 +3,8 @@
 // nn.MultiheadAttention of the text tower (:140-146,447-453).
 //
 // One CTA per (clip, head, PAIR of 128-row query tiles).  Roles:
-//   warps 0-3 / 4-7 : softmax group 0 / 1 (one query row per thread: S tile read from TMEM, online softmax in fp32
-//                     registers, P written to swizzled smem as bf16, O accumulated in registers)
+//   warps 0-3 / 4-7 : softmax group 0 / 1 (one query row per thread: S row read once from TMEM, online softmax in fp32
+//                     registers with lazy rescaling, P written to swizzled smem as bf16, O accumulated in TMEM)
 //   warp 8          : MMA issuer  (S_w = Q_w K_j^T and O_w = P_w V_j on tcgen05, accumulators in TMEM)
 //   warp 9          : TMA producer (Q tiles once, then a 3-stage K/V ring shared by both groups)
 // The two groups ping-pong: while one does softmax (MUFU/FMA bound at head dim 64) the other's MMAs run.
@@ -14,18 +14,17 @@
 namespace {
 using namespace avn;
 
-constexpr int TILE = 128, HD = 64, KV_STAGES = 3;
-constexpr int NTHREADS = 320;
+constexpr int TILE = 128, HD = 64, KV_STAGES = 4;
+constexpr int NTHREADS = 384;     // warps 0-7 math, 8 MMA issuer, 9 TMA producer, 10-11 idle (complete the warpgroup)
 constexpr int Q_BYTES = TILE * HD * 2;            // 16 KB
 constexpr int KV_BYTES = TILE * HD * 2;           // 16 KB each for K and V
-constexpr int P_BYTES = TILE * TILE * 2;          // 32 KB
 constexpr int OFF_Q = 0;
 constexpr int OFF_K = OFF_Q + 2 * Q_BYTES;
 constexpr int OFF_V = OFF_K + KV_STAGES * KV_BYTES;
-constexpr int OFF_P = OFF_V + KV_STAGES * KV_BYTES;
-constexpr int OFF_BAR = OFF_P + 2 * P_BYTES;
+constexpr int OFF_BAR = OFF_V + KV_STAGES * KV_BYTES;
 constexpr int SMEM_TOTAL = OFF_BAR + 256 + 1024;
-constexpr uint32_t TM_S = 0, TM_O = 256;          // TMEM columns: S_w at w*128, O_w at 256 + w*64
+// TMEM columns: S_w (fp32) at w*128, O_w (fp32) at 256 + w*64, P_w (bf16 pairs, the A operand of P V) at 384 + w*64
+constexpr uint32_t TM_S = 0, TM_O = 256, TM_P = 384;
 
 struct Bars {
     uint64_t q_full;
@@ -33,6 +32,46 @@ struct Bars {
     uint64_t s_full[2], s_free[2], p_ready[2], o_full[2];
     uint32_t tmem_ptr;
 };
+
+
+template <bool MASK>
+__device__ __forceinline__ float row_max(const uint32_t* sv, int limit) {
+    float a = -INFINITY, b = -INFINITY, c = -INFINITY, d = -INFINITY;     // four independent chains
+#pragma unroll
+    for (int i = 0; i < TILE; i += 4) {
+        float v0 = __uint_as_float(sv[i]), v1 = __uint_as_float(sv[i + 1]), v2 = __uint_as_float(sv[i + 2]), v3 = __uint_as_float(sv[i + 3]);
+        if (MASK) {
+            if (i >= limit) v0 = -INFINITY;
+            if (i + 1 >= limit) v1 = -INFINITY;
+            if (i + 2 >= limit) v2 = -INFINITY;
+            if (i + 3 >= limit) v3 = -INFINITY;
+        }
+        a = fmaxf(a, v0); b = fmaxf(b, v1); c = fmaxf(c, v2); d = fmaxf(d, v3);
+    }
+    return fmaxf(fmaxf(a, b), fmaxf(c, d));
+}
+
+// p = exp2(s * scale_log2 - m_ref) for one row of 128 scores -> packed bf16 pairs; returns the row sum
+template <bool MASK>
+__device__ __forceinline__ float row_exp(const uint32_t* sv, uint32_t* pk, float scale_log2, float m_ref, int limit) {
+    const float2 sc2 = make_float2(scale_log2, scale_log2), nm2 = make_float2(-m_ref, -m_ref);
+    float2 r0 = make_float2(0.f, 0.f), r1 = make_float2(0.f, 0.f);
+#pragma unroll
+    for (int i = 0; i < TILE / 2; i += 2) {
+        const float2 x0 = __ffma2_rn(make_float2(__uint_as_float(sv[2 * i]), __uint_as_float(sv[2 * i + 1])), sc2, nm2);
+        const float2 x1 = __ffma2_rn(make_float2(__uint_as_float(sv[2 * i + 2]), __uint_as_float(sv[2 * i + 3])), sc2, nm2);
+        float2 e0 = make_float2(ex2(x0.x), ex2(x0.y)), e1 = make_float2(ex2(x1.x), ex2(x1.y));
+        if (MASK) {
+            if (2 * i >= limit) e0.x = 0.f;
+            if (2 * i + 1 >= limit) e0.y = 0.f;
+            if (2 * i + 2 >= limit) e1.x = 0.f;
+            if (2 * i + 3 >= limit) e1.y = 0.f;
+        }
+        r0 = __fadd2_rn(r0, e0); r1 = __fadd2_rn(r1, e1);
+        pk[i] = pack_bf16(e0.x, e0.y); pk[i + 1] = pack_bf16(e1.x, e1.y);
+    }
+    return (r0.x + r0.y) + (r1.x + r1.y);
+}
 
 __global__ void __launch_bounds__(NTHREADS, 1)
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmO, float* __restrict__ lse,
@@ -67,8 +106,12 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
     tc_fence_after();
     const uint32_t tmem_base = bars->tmem_ptr;
 
-    if (warp == 9) {
+    // the 8 math warps take the registers of the control warpgroup (setmaxnreg is per warpgroup: warps 8-11 all shrink)
+    if (warp >= 10) {
+        reg_dec<40>();       // idle warps: only complete the third warpgroup
+    } else if (warp == 9) {
         // ===================== TMA producer =====================
+        reg_dec<40>();
         if (lane == 0) {
             const int n_q = (qt[1] < q_tiles) ? 2 : 1;
             mbar_expect_tx(&bars->q_full, n_q * Q_BYTES);
@@ -83,6 +126,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
         }
     } else if (warp == 8) {
         // ===================== MMA issuer =====================
+        reg_dec<40>();
         if (lane == 0 && nkv_max > 0) {
             constexpr uint32_t idesc_s = umma_idesc_bf16(TILE, TILE, false, false);
             constexpr uint32_t idesc_o = umma_idesc_bf16(TILE, HD, false, true);
@@ -112,11 +156,10 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
                     if (j >= nkv[w]) continue;
                     mbar_wait(&bars->p_ready[w], j & 1);
                     tc_fence_after();
-                    const uint32_t pa = smem_u32(smem + OFF_P + w * P_BYTES);
 #pragma unroll
-                    for (int k = 0; k < TILE / 16; ++k)
-                        umma_ss(tmem_base + TM_O + w * HD, umma_smem_desc(pa + (k >> 2) * (P_BYTES / 2) + (k & 3) * 32, 16, 1024),
-                                umma_smem_desc(va + k * 2048, 8192, 1024), idesc_o, k > 0 ? 1u : 0u);
+                    for (int k = 0; k < TILE / 16; ++k)      // O_w += P_w V_j : A = P from TMEM (8 columns per K=16), B = V (MN-major)
+                        umma_ts(tmem_base + TM_O + w * HD, tmem_base + TM_P + w * 64 + k * 8, umma_smem_desc(va + k * 2048, 8192, 1024),
+                                idesc_o, (j > 0 || k > 0) ? 1u : 0u);
                     umma_commit(&bars->o_full[w]);
                 }
                 umma_commit(&bars->kv_empty[st]);
@@ -124,6 +167,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
         }
     } else {
         // ===================== softmax groups =====================
+        reg_inc<232>();
         const int w = warp >> 2;
         const int row = (warp & 3) * 32 + lane;
         const int n_my = nkv[w];
@@ -132,94 +176,71 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
             const int qrow = q0 + row;
             const uint32_t t_s = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + TM_S + w * TILE;
             const uint32_t t_o = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + TM_O + w * HD;
-            uint8_t* sP = smem + OFF_P + w * P_BYTES;
-            float2 o2[HD / 2];                       // O accumulator, kept one rescale behind (relative to the previous maximum)
-#pragma unroll
-            for (int i = 0; i < HD / 2; ++i) o2[i] = make_float2(0.f, 0.f);
-            float m = -INFINITY, l = 0.f, alpha_prev = 1.f;
-            const float2 sc2 = make_float2(scale_log2, scale_log2);
+            const uint32_t t_p = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + TM_P + w * 64;
+            uint8_t* sO = smem + OFF_Q + w * Q_BYTES;      // O staging for the TMA store: this group's Q tile is dead by then
+            // O accumulates in TMEM across K/V tiles (the MMA adds P_j V_j).  The softmax reference m_ref is only raised
+            // when the running row maximum grows by more than 2^8 (lazy rescaling): then O (in TMEM) and l are rescaled.
+            float m_ref = -INFINITY, l = 0.f;
             for (int j = 0; j < n_my; ++j) {
                 const int kv0 = j * TILE;
                 const bool need_mask = (kv0 + TILE > S) || (causal && kv0 + TILE - 1 > q0);
                 const int limit = causal ? min(S - kv0, qrow - kv0 + 1) : (S - kv0);   // columns [0, limit) are valid
                 mbar_wait(&bars->s_full[w], j & 1);
                 tc_fence_after();
-                // pass 1: row maximum
-                float mx = -INFINITY;
+                uint32_t sv[TILE];                 // this thread's row of S: one TMEM read, then S is handed back at once
 #pragma unroll
-                for (int c = 0; c < 4; ++c) {
-                    uint32_t v[32];
-                    tmem_ld32(t_s + c * 32, v);
-                    tmem_ld_wait();
-                    if (need_mask) {
-#pragma unroll
-                        for (int i = 0; i < 32; ++i) if (c * 32 + i < limit) mx = fmaxf(mx, __uint_as_float(v[i]));
-                    } else {
-#pragma unroll
-                        for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(v[i]));
-                    }
-                }
-                const float m_new = fmaxf(m, mx * scale_log2);
-                const float alpha = ex2(m - m_new);
-                // fold the previous tile's P*V into the register accumulator: o = o * alpha_prev + PV_{j-1}
-                // (waiting for P*V of tile j-1 here also guarantees that the MMA has finished READING this group's P
-                //  buffer, which pass 2 is about to overwrite)
+                for (int c = 0; c < 4; ++c) tmem_ld32(t_s + c * 32, sv + c * 32);
+                tmem_ld_wait();
+                tc_fence_before();
+                mbar_arrive(&bars->s_free[w]);      // the MMA warp may now overwrite S with Q K_{j+1}^T
+                const float mx = need_mask ? row_max<true>(sv, limit) : row_max<false>(sv, limit);
+                const float mxs = mx * scale_log2;
+                const bool raise = mxs > m_ref + 8.0f;
+                const float m_new = raise ? mxs : m_ref;
+                const float alpha = raise ? ex2(m_ref - m_new) : 1.0f;
+                const bool fix_o = (j > 0) && __any_sync(0xffffffffu, raise);
+                m_ref = m_new;
+                uint32_t pk[TILE / 2];
+                float rs;
+                if (need_mask) rs = row_exp<true>(sv, pk, scale_log2, m_ref, limit);
+                else rs = row_exp<false>(sv, pk, scale_log2, m_ref, limit);
+                l = fmaf(l, alpha, rs);
+                // P V of tile j-1 must have completed: the MMA has finished reading this group's P buffer and O is stable
                 if (j > 0) {
                     mbar_wait(&bars->o_full[w], (j - 1) & 1);
                     tc_fence_after();
-                    const float2 a2 = make_float2(alpha_prev, alpha_prev);
+                    if (fix_o) {                     // warp-uniform; rows whose reference did not move use alpha = 1
+                        const float2 a2 = make_float2(alpha, alpha);
 #pragma unroll
-                    for (int c = 0; c < 2; ++c) {
-                        uint32_t v[32];
-                        tmem_ld32(t_o + c * 32, v);
-                        tmem_ld_wait();
+                        for (int c = 0; c < 2; ++c) {
+                            uint32_t v[32];
+                            tmem_ld32(t_o + c * 32, v);
+                            tmem_ld_wait();
 #pragma unroll
-                        for (int i = 0; i < 16; ++i)
-                            o2[c * 16 + i] = __ffma2_rn(o2[c * 16 + i], a2, make_float2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1])));
-                    }
-                    tc_fence_before();
-                }
-                alpha_prev = alpha;
-                // pass 2: probabilities -> bf16 -> smem (two K-major 128B-swizzled [128][64] sub-tiles)
-                const float2 nm2 = make_float2(-m_new, -m_new);
-                float2 rs2 = make_float2(0.f, 0.f);
-#pragma unroll
-                for (int c = 0; c < 4; ++c) {
-                    uint32_t v[32];
-                    tmem_ld32(t_s + c * 32, v);
-                    tmem_ld_wait();
-                    if (c == 3) { tc_fence_before(); mbar_arrive(&bars->s_free[w]); }
-                    uint32_t pk[16];
-#pragma unroll
-                    for (int i = 0; i < 16; ++i) {
-                        const float2 x = __ffma2_rn(make_float2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1])), sc2, nm2);
-                        float2 e = make_float2(ex2(x.x), ex2(x.y));
-                        if (need_mask) {
-                            if (c * 32 + 2 * i >= limit) e.x = 0.f;
-                            if (c * 32 + 2 * i + 1 >= limit) e.y = 0.f;
+                            for (int i = 0; i < 16; ++i) {
+                                const float2 r = __fmul2_rn(make_float2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1])), a2);
+                                v[2 * i] = __float_as_uint(r.x); v[2 * i + 1] = __float_as_uint(r.y);
+                            }
+                            tmem_st32(t_o + c * 32, v);
                         }
-                        rs2 = __fadd2_rn(rs2, e);
-                        pk[i] = pack_bf16(e.x, e.y);
-                    }
-                    uint8_t* sub = sP + (c >> 1) * (P_BYTES / 2) + row * 128;
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        const int c16 = (c & 1) * 4 + i;
-                        *(uint4*)(sub + ((c16 ^ (row & 7)) << 4)) = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+                        tmem_st_wait();
                     }
                 }
-                l = fmaf(l, alpha, rs2.x + rs2.y);
-                m = m_new;
-                fence_proxy_async_smem();
+                // P -> TMEM as packed bf16 pairs (row = lane, 64 columns): the MMA reads it as its A operand
+                tmem_st32(t_p, pk);
+                tmem_st32(t_p + 32, pk + 32);
+                tmem_st_wait();
+                tc_fence_before();
                 mbar_arrive(&bars->p_ready[w]);
             }
-            // last tile's P*V
+            // all P V accumulated
             mbar_wait(&bars->o_full[w], (n_my - 1) & 1);
             tc_fence_after();
             const float inv_l = 1.f / l;
+            const float m = m_ref;
             float o[HD];
             {
-                const float2 a2 = make_float2(alpha_prev, alpha_prev), il2 = make_float2(inv_l, inv_l);
+                const float2 il2 = make_float2(inv_l, inv_l);
 #pragma unroll
                 for (int c = 0; c < 2; ++c) {
                     uint32_t v[32];
@@ -227,14 +248,14 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
                     tmem_ld_wait();
 #pragma unroll
                     for (int i = 0; i < 16; ++i) {
-                        const float2 r = __fmul2_rn(__ffma2_rn(o2[c * 16 + i], a2, make_float2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]))), il2);
+                        const float2 r = __fmul2_rn(make_float2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1])), il2);
                         o[c * 32 + 2 * i] = r.x; o[c * 32 + 2 * i + 1] = r.y;
                     }
                 }
             }
             if (qrow < S) lse[((long long)b * H + h) * S + qrow] = (m + log2f(l)) * 0.6931471805599453f;
-            // O tile -> swizzled smem (reuses this group's P buffer: its last MMA has completed) -> TMA store
-            uint8_t* stg = sP + row * 128;
+            // O tile -> swizzled smem (reuses this group's Q buffer: every MMA has completed) -> TMA store
+            uint8_t* stg = sO + row * 128;
 #pragma unroll
             for (int i = 0; i < 8; ++i)
                 *(uint4*)(stg + ((i ^ (row & 7)) << 4)) =
@@ -243,7 +264,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
             fence_proxy_async_smem();
             named_bar_sync(1 + w, 128);
             if ((threadIdx.x & 127) == 0) {
-                tma_store_3d(&tmO, sP, h * HD, q0, b);
+                tma_store_3d(&tmO, sO, h * HD, q0, b);
                 tma_commit_group();
                 tma_wait_group0();
             }
