@@ -87,23 +87,29 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
         reg_dec<40>();       // idle warps: only complete the third warpgroup
     } else if (warp == 9) {
         // ===================== TMA producer =====================
+        // (whole warp loops and waits; one elected lane issues, so addresses and coordinates stay in uniform registers)
         reg_dec<40>();
-        if (lane == 0) {
+        if (elect_one()) {
             mbar_expect_tx(&bars->kv_full, 2 * T16);
             tma_load_3d(smem + OFF_K, &tmQKV, &bars->kv_full, (H + h) * HD, kv0, b);
             tma_load_3d(smem + OFF_V, &tmQKV, &bars->kv_full, (2 * H + h) * HD, kv0, b);
-            for (int t = 0; t < n_i; ++t) {
-                const int st = t & 1;
-                mbar_wait(&bars->qdo_empty[st], ((t >> 1) & 1) ^ 1);
+        }
+        __syncwarp();
+        for (int t = 0; t < n_i; ++t) {
+            const int st = t & 1;
+            mbar_wait(&bars->qdo_empty[st], ((t >> 1) & 1) ^ 1);
+            if (elect_one()) {
                 mbar_expect_tx(&bars->qdo_full[st], 2 * T16);
                 tma_load_3d(smem + OFF_Q + st * T16, &tmQKV, &bars->qdo_full[st], h * HD, (i0 + t) * TILE, b);
                 tma_load_3d(smem + OFF_DO + st * T16, &tmDO, &bars->qdo_full[st], h * HD, (i0 + t) * TILE, b);
             }
+            __syncwarp();
         }
     } else if (warp == 8) {
         // ===================== MMA issuer =====================
+        // waits are executed by the whole warp, the MMAs by one elected lane (descriptors stay in uniform registers)
         reg_dec<40>();
-        if (lane == 0 && n_i > 0) {
+        if (n_i > 0) {
             constexpr uint32_t idesc_s = umma_idesc_bf16(TILE, TILE, false, false);
             constexpr uint32_t idesc_dkv = umma_idesc_bf16(TILE, HD, true, true);
             constexpr uint32_t idesc_dq = umma_idesc_bf16(TILE, HD, false, true);
@@ -113,14 +119,17 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
                 mbar_wait(&bars->qdo_full[st], (t >> 1) & 1);
                 if (t > 0) mbar_wait(&bars->sdp_free, (t - 1) & 1);
                 tc_fence_after();
-                const uint32_t qa = smem_u32(smem + OFF_Q + st * T16), doa = smem_u32(smem + OFF_DO + st * T16);
+                if (elect_one()) {
+                    const uint32_t qa = smem_u32(smem + OFF_Q + st * T16), doa = smem_u32(smem + OFF_DO + st * T16);
 #pragma unroll
-                for (int k = 0; k < HD / 16; ++k)
-                    umma_ss(tmem_base + TM_S, umma_smem_desc(qa + k * 32, 16, 1024), umma_smem_desc(ka + k * 32, 16, 1024), idesc_s, k > 0);
+                    for (int k = 0; k < HD / 16; ++k)
+                        umma_ss(tmem_base + TM_S, umma_smem_desc(qa + k * 32, 16, 1024), umma_smem_desc(ka + k * 32, 16, 1024), idesc_s, k > 0);
 #pragma unroll
-                for (int k = 0; k < HD / 16; ++k)
-                    umma_ss(tmem_base + TM_DP, umma_smem_desc(doa + k * 32, 16, 1024), umma_smem_desc(va + k * 32, 16, 1024), idesc_s, k > 0);
-                umma_commit(&bars->sdp_full);
+                    for (int k = 0; k < HD / 16; ++k)
+                        umma_ss(tmem_base + TM_DP, umma_smem_desc(doa + k * 32, 16, 1024), umma_smem_desc(va + k * 32, 16, 1024), idesc_s, k > 0);
+                    umma_commit(&bars->sdp_full);
+                }
+                __syncwarp();
             };
             mbar_wait(&bars->kv_full, 0);
             issue_sdp(0);
@@ -131,21 +140,27 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
                 tc_fence_after();
                 const uint32_t qa = smem_u32(smem + OFF_Q + st * T16), doa = smem_u32(smem + OFF_DO + st * T16);
                 const uint32_t pa = smem_u32(smem + OFF_P + st * 2 * T16), dsa = smem_u32(smem + OFF_DS + st * 2 * T16);
+                if (elect_one()) {
 #pragma unroll
-                for (int k = 0; k < TILE / 16; ++k)      // dV += P^T dO   (A = P as MN-major, B = dO as MN-major)
-                    umma_ss(tmem_base + TM_DV, umma_smem_desc(pa + k * 2048, 16384, 1024), umma_smem_desc(doa + k * 2048, 8192, 1024),
-                            idesc_dkv, (t > 0 || k > 0) ? 1u : 0u);
+                    for (int k = 0; k < TILE / 16; ++k)      // dV += P^T dO   (A = P as MN-major, B = dO as MN-major)
+                        umma_ss(tmem_base + TM_DV, umma_smem_desc(pa + k * 2048, 16384, 1024), umma_smem_desc(doa + k * 2048, 8192, 1024),
+                                idesc_dkv, (t > 0 || k > 0) ? 1u : 0u);
 #pragma unroll
-                for (int k = 0; k < TILE / 16; ++k)      // dK += dS^T Q
-                    umma_ss(tmem_base + TM_DK, umma_smem_desc(dsa + k * 2048, 16384, 1024), umma_smem_desc(qa + k * 2048, 8192, 1024),
-                            idesc_dkv, (t > 0 || k > 0) ? 1u : 0u);
+                    for (int k = 0; k < TILE / 16; ++k)      // dK += dS^T Q
+                        umma_ss(tmem_base + TM_DK, umma_smem_desc(dsa + k * 2048, 16384, 1024), umma_smem_desc(qa + k * 2048, 8192, 1024),
+                                idesc_dkv, (t > 0 || k > 0) ? 1u : 0u);
+                }
+                __syncwarp();
                 if (t > 0) { mbar_wait(&bars->dq_free, (t - 1) & 1); tc_fence_after(); }   // dQ_{t-1} has left TMEM
+                if (elect_one()) {
 #pragma unroll
-                for (int k = 0; k < TILE / 16; ++k)      // dQ_i = dS K_j  (A = dS K-major, B = K_j as MN-major)
-                    umma_ss(tmem_base + TM_DQ, umma_smem_desc(dsa + (k >> 2) * 16384 + (k & 3) * 32, 16, 1024),
-                            umma_smem_desc(ka + k * 2048, 8192, 1024), idesc_dq, k > 0 ? 1u : 0u);
-                umma_commit(&bars->dq_full);
-                umma_commit(&bars->qdo_empty[st]);
+                    for (int k = 0; k < TILE / 16; ++k)      // dQ_i = dS K_j  (A = dS K-major, B = K_j as MN-major)
+                        umma_ss(tmem_base + TM_DQ, umma_smem_desc(dsa + (k >> 2) * 16384 + (k & 3) * 32, 16, 1024),
+                                umma_smem_desc(ka + k * 2048, 8192, 1024), idesc_dq, k > 0 ? 1u : 0u);
+                    umma_commit(&bars->dq_full);
+                    umma_commit(&bars->qdo_empty[st]);
+                }
+                __syncwarp();
             }
         }
     } else {
@@ -171,7 +186,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
             uint8_t* stg = smem + OFF_P + (t & 1) * 2 * T16 + half * T16;
 #pragma unroll
             for (int i = 0; i < 8; ++i)
-                *(uint4*)(stg + row * 128 + ((i ^ (row & 7)) << 4)) = make_uint4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+                st_shared_v4(stg + row * 128 + ((i ^ (row & 7)) << 4), make_uint4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]));
             fence_proxy_async_smem();
             named_bar_sync(1 + half, 128);
             if (leader) { tma_reduce_add_3d(&tmDQ, stg, h * HD + half * 32, (i0 + t) * TILE, b); tma_commit_group(); }
@@ -216,8 +231,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
                 const int off = (i ^ (row & 7)) << 4;
-                *(uint4*)(prow + off) = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
-                *(uint4*)(drow + off) = make_uint4(dsk[4 * i], dsk[4 * i + 1], dsk[4 * i + 2], dsk[4 * i + 3]);
+                st_shared_v4(prow + off, make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]));
+                st_shared_v4(drow + off, make_uint4(dsk[4 * i], dsk[4 * i + 1], dsk[4 * i + 2], dsk[4 * i + 3]));
             }
             fence_proxy_async_smem();
             mbar_arrive(&bars->pds_ready);
@@ -236,14 +251,14 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
                 const int off = ((half * 4 + i) ^ (row & 7)) << 4;
-                *(uint4*)(vrow + off) = make_uint4(pack_bf16(__uint_as_float(v[8 * i]), __uint_as_float(v[8 * i + 1])),
+                st_shared_v4(vrow + off, make_uint4(pack_bf16(__uint_as_float(v[8 * i]), __uint_as_float(v[8 * i + 1])),
                                                    pack_bf16(__uint_as_float(v[8 * i + 2]), __uint_as_float(v[8 * i + 3])),
                                                    pack_bf16(__uint_as_float(v[8 * i + 4]), __uint_as_float(v[8 * i + 5])),
-                                                   pack_bf16(__uint_as_float(v[8 * i + 6]), __uint_as_float(v[8 * i + 7])));
-                *(uint4*)(krow + off) = make_uint4(pack_bf16(__uint_as_float(k[8 * i]), __uint_as_float(k[8 * i + 1])),
+                                                   pack_bf16(__uint_as_float(v[8 * i + 6]), __uint_as_float(v[8 * i + 7]))));
+                st_shared_v4(krow + off, make_uint4(pack_bf16(__uint_as_float(k[8 * i]), __uint_as_float(k[8 * i + 1])),
                                                    pack_bf16(__uint_as_float(k[8 * i + 2]), __uint_as_float(k[8 * i + 3])),
                                                    pack_bf16(__uint_as_float(k[8 * i + 4]), __uint_as_float(k[8 * i + 5])),
-                                                   pack_bf16(__uint_as_float(k[8 * i + 6]), __uint_as_float(k[8 * i + 7])));
+                                                   pack_bf16(__uint_as_float(k[8 * i + 6]), __uint_as_float(k[8 * i + 7]))));
             }
             fence_proxy_async_smem();
             named_bar_sync(3, 256);

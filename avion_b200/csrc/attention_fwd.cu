@@ -111,34 +111,43 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
         reg_dec<40>();       // idle warps: only complete the third warpgroup
     } else if (warp == 9) {
         // ===================== TMA producer =====================
+        // (the whole warp runs the loop and one elected lane issues, so addresses and coordinates stay in uniform registers)
         reg_dec<40>();
-        if (lane == 0) {
-            const int n_q = (qt[1] < q_tiles) ? 2 : 1;
+        const int n_q = (qt[1] < q_tiles) ? 2 : 1;
+        if (elect_one()) {
             mbar_expect_tx(&bars->q_full, n_q * Q_BYTES);
             for (int w = 0; w < n_q; ++w) tma_load_3d(smem + OFF_Q + w * Q_BYTES, &tmQKV, &bars->q_full, h * HD, qt[w] * TILE, b);
-            for (int j = 0; j < nkv_max; ++j) {
-                const int st = j % KV_STAGES;
-                mbar_wait(&bars->kv_empty[st], ((j / KV_STAGES) & 1) ^ 1);
+        }
+        __syncwarp();
+        for (int j = 0; j < nkv_max; ++j) {
+            const int st = j % KV_STAGES;
+            mbar_wait(&bars->kv_empty[st], ((j / KV_STAGES) & 1) ^ 1);
+            if (elect_one()) {
                 mbar_expect_tx(&bars->kv_full[st], 2 * KV_BYTES);
                 tma_load_3d(smem + OFF_K + st * KV_BYTES, &tmQKV, &bars->kv_full[st], (H + h) * HD, j * TILE, b);
                 tma_load_3d(smem + OFF_V + st * KV_BYTES, &tmQKV, &bars->kv_full[st], (2 * H + h) * HD, j * TILE, b);
             }
+            __syncwarp();
         }
     } else if (warp == 8) {
         // ===================== MMA issuer =====================
         reg_dec<40>();
-        if (lane == 0 && nkv_max > 0) {
+        if (nkv_max > 0) {
             constexpr uint32_t idesc_s = umma_idesc_bf16(TILE, TILE, false, false);
             constexpr uint32_t idesc_o = umma_idesc_bf16(TILE, HD, false, true);
+            // waits are executed by the whole warp, the MMAs by one elected lane (descriptors stay in uniform registers)
             auto issue_s = [&](int w, int j) {
                 if (j > 0) { mbar_wait(&bars->s_free[w], (j - 1) & 1); tc_fence_after(); }
-                const uint32_t qa = smem_u32(smem + OFF_Q + w * Q_BYTES);
-                const uint32_t ka = smem_u32(smem + OFF_K + (j % KV_STAGES) * KV_BYTES);
+                if (elect_one()) {
+                    const uint32_t qa = smem_u32(smem + OFF_Q + w * Q_BYTES);
+                    const uint32_t ka = smem_u32(smem + OFF_K + (j % KV_STAGES) * KV_BYTES);
 #pragma unroll
-                for (int k = 0; k < HD / 16; ++k)
-                    umma_ss(tmem_base + TM_S + w * TILE, umma_smem_desc(qa + k * 32, 16, 1024), umma_smem_desc(ka + k * 32, 16, 1024),
-                            idesc_s, k > 0 ? 1u : 0u);
-                umma_commit(&bars->s_full[w]);
+                    for (int k = 0; k < HD / 16; ++k)
+                        umma_ss(tmem_base + TM_S + w * TILE, umma_smem_desc(qa + k * 32, 16, 1024), umma_smem_desc(ka + k * 32, 16, 1024),
+                                idesc_s, k > 0 ? 1u : 0u);
+                    umma_commit(&bars->s_full[w]);
+                }
+                __syncwarp();
             };
             mbar_wait(&bars->q_full, 0);
             mbar_wait(&bars->kv_full[0], 0);
@@ -151,18 +160,22 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
                     tc_fence_after();
                     for (int w = 0; w < 2; ++w) if (j + 1 < nkv[w]) issue_s(w, j + 1);
                 }
-                const uint32_t va = smem_u32(smem + OFF_V + st * KV_BYTES);
                 for (int w = 0; w < 2; ++w) {
                     if (j >= nkv[w]) continue;
                     mbar_wait(&bars->p_ready[w], j & 1);
                     tc_fence_after();
+                    if (elect_one()) {
+                        const uint32_t va = smem_u32(smem + OFF_V + st * KV_BYTES);
 #pragma unroll
-                    for (int k = 0; k < TILE / 16; ++k)      // O_w += P_w V_j : A = P from TMEM (8 columns per K=16), B = V (MN-major)
-                        umma_ts(tmem_base + TM_O + w * HD, tmem_base + TM_P + w * 64 + k * 8, umma_smem_desc(va + k * 2048, 8192, 1024),
-                                idesc_o, (j > 0 || k > 0) ? 1u : 0u);
-                    umma_commit(&bars->o_full[w]);
+                        for (int k = 0; k < TILE / 16; ++k)      // O_w += P_w V_j : A = P from TMEM (8 columns per K=16), B = V (MN-major)
+                            umma_ts(tmem_base + TM_O + w * HD, tmem_base + TM_P + w * 64 + k * 8, umma_smem_desc(va + k * 2048, 8192, 1024),
+                                    idesc_o, (j > 0 || k > 0) ? 1u : 0u);
+                        umma_commit(&bars->o_full[w]);
+                    }
+                    __syncwarp();
                 }
-                umma_commit(&bars->kv_empty[st]);
+                if (elect_one()) umma_commit(&bars->kv_empty[st]);
+                __syncwarp();
             }
         }
     } else {
@@ -258,9 +271,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
             uint8_t* stg = sO + row * 128;
 #pragma unroll
             for (int i = 0; i < 8; ++i)
-                *(uint4*)(stg + ((i ^ (row & 7)) << 4)) =
-                    make_uint4(pack_bf16(o[8 * i], o[8 * i + 1]), pack_bf16(o[8 * i + 2], o[8 * i + 3]),
-                               pack_bf16(o[8 * i + 4], o[8 * i + 5]), pack_bf16(o[8 * i + 6], o[8 * i + 7]));
+                st_shared_v4(stg + ((i ^ (row & 7)) << 4), make_uint4(pack_bf16(o[8 * i], o[8 * i + 1]), pack_bf16(o[8 * i + 2], o[8 * i + 3]),
+                               pack_bf16(o[8 * i + 4], o[8 * i + 5]), pack_bf16(o[8 * i + 6], o[8 * i + 7])));
             fence_proxy_async_smem();
             named_bar_sync(1 + w, 128);
             if ((threadIdx.x & 127) == 0) {

@@ -43,6 +43,20 @@ namespace avn {
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }
 
+// One lane of a converged warp, chosen by the hardware.  Unlike `lane == 0`, the compiler knows the guarded region is
+// warp-uniform, so tcgen05/TMA operands stay in uniform registers (no per-instruction ELECT/R2UR.BROADCAST waterfall).
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
+
+// 16-byte shared-memory store with the state space spelled out (the 1024-byte alignment round-trip of the dynamic smem
+// base hides it from the compiler, which would otherwise emit generic ST.E.128)
+__device__ __forceinline__ void st_shared_v4(void* p, uint4 v) {
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(smem_u32(p)), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
 // ---- mbarrier ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");

@@ -127,7 +127,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             for (int kb = kb0; kb < kb1; ++kb) {
                 mbar_wait(&full_bar[stage], phase);
                 tc_fence_after();
-                if (lane == 0) {
+                if (elect_one()) {
                     const uint32_t a_addr = smem_u32(sA + stage * A_STAGE_BYTES);
                     const uint32_t b_addr = smem_u32(sB + stage * L::B_STAGE_BYTES);
 #pragma unroll
@@ -188,7 +188,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 #pragma unroll
                     for (int i = 0; i < 8; ++i) {
                         uint4 w = make_uint4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
-                        *(uint4*)(stg + row * 128 + ((i ^ (row & 7)) << 4)) = w;
+                        st_shared_v4(stg + row * 128 + ((i ^ (row & 7)) << 4), w);
                     }
                     fence_proxy_async_smem();
                     named_bar_sync(bar_id, 128);
@@ -233,7 +233,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                         uint4 w = make_uint4(pack_bf16(f[8 * i], f[8 * i + 1]), pack_bf16(f[8 * i + 2], f[8 * i + 3]),
                                              pack_bf16(f[8 * i + 4], f[8 * i + 5]), pack_bf16(f[8 * i + 6], f[8 * i + 7]));
                         const int c16 = (u & 1) * 4 + i;
-                        *(uint4*)(stg + row * 128 + ((c16 ^ (row & 7)) << 4)) = w;
+                        st_shared_v4(stg + row * 128 + ((c16 ^ (row & 7)) << 4), w);
                     }
                     if ((u & 1) == 1) {
                         fence_proxy_async_smem();
@@ -245,7 +245,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 #pragma unroll
                             for (int i = 0; i < 8; ++i) {
                                 uint4 w = make_uint4(keep[4 * i], keep[4 * i + 1], keep[4 * i + 2], keep[4 * i + 3]);
-                                *(uint4*)(stg + row * 128 + ((i ^ (row & 7)) << 4)) = w;
+                                st_shared_v4(stg + row * 128 + ((i ^ (row & 7)) << 4), w);
                             }
                             fence_proxy_async_smem();
                             named_bar_sync(bar_id, 128);
