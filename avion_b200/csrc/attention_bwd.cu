@@ -1,13 +1,15 @@
 // V4 backward: flash-style attention backward on tcgen05, head dim 64.
 // Replaces the backward of flash_attn_qkvpacked_func (avion/models/transformer.py:148) / nn.MultiheadAttention (:140-146).
 //
-// One CTA per (clip, head, 128-row K/V tile j); it loops over the query tiles i and issues five MMAs per (i, j):
-//   S  = Q_i K_j^T          dP = dO_i V_j^T                          (recompute; TMEM, 128 columns each)
-//   dV += P^T dO_i          dK += dS^T Q_i                           (accumulate in TMEM across i, 64 columns each)
+// One CTA per (clip, head, 128-row K/V tile j); it loops over the query tiles i.  Everything is computed TRANSPOSED
+// (key rows on the TMEM lanes) so that P^T can feed the dV MMA straight from TMEM and dS^T is written to smem once:
+//   S^T  = K_j Q_i^T         dP^T = V_j dO_i^T                       (recompute; TMEM, 128 fp32 columns each)
+//   P^T  = exp(scale*S^T - LSE_q)           -> TMEM as bf16 (A operand of dV)
+//   dS^T = scale * P^T o (dP^T - delta_q)   -> smem [kv][q] bf16 (K-major A of dK, MN-major A of dQ: same bytes)
+//   dV  += P^T dO_i          dK += dS^T Q_i                           (accumulate in TMEM across i, 64 columns each)
 //   dQ_i(partial) = dS K_j                                           (TMEM -> fp32 smem -> TMA reduce-add into dq_acc)
-// with P = exp(scale*S - LSE), dS = scale * P o (dP - delta) computed by 8 warps (thread = (query row, column half)).
-// P and dS are written once to 128B-swizzled smem as [q][kv] bf16 and consumed both as a K-major A operand (dQ) and as
-// an MN-major A operand (P^T, dS^T) - the same bytes, two descriptors.
+// Warp roles (16 warps): 0-7 compute (thread = key row x half of the 128 query columns), 8-11 dQ drain,
+// 12 MMA issuer, 13 TMA producer, 14-15 idle (complete the warpgroup for setmaxnreg).
 #include "common.cuh"
 #include "../../include/avion_b200.h"
 
@@ -15,42 +17,49 @@ namespace {
 using namespace avn;
 
 constexpr int TILE = 128, HD = 64;
-constexpr int NTHREADS = 384;     // warps 0-7 math, 8 MMA issuer, 9 TMA producer, 10-11 idle (complete the warpgroup)
+constexpr int NTHREADS = 512;
 constexpr int T16 = TILE * HD * 2;                // 16 KB: one [128][64] bf16 tile
 constexpr int OFF_K = 0, OFF_V = T16;
-constexpr int OFF_Q = 2 * T16;                    // 2 stages
-constexpr int OFF_DO = 4 * T16;                   // 2 stages
-constexpr int OFF_P = 6 * T16;                    // 2 buffers x 32 KB ([q][kv] bf16, two 64-column sub-tiles each)
-constexpr int OFF_DS = 10 * T16;                  // 2 buffers x 32 KB
-constexpr int OFF_BAR = 14 * T16;
-constexpr int SMEM_TOTAL = OFF_BAR + 256 + 1024;
-constexpr uint32_t TM_S = 0, TM_DP = 128, TM_DV = 256, TM_DK = 320, TM_DQ = 384;
-// The P buffer of tile t doubles as the fp32 staging tile of dQ_t once the MMAs of tile t have completed.
+constexpr int QDO_STAGES = 3;                     // the TMA latency of a Q/dO tile pair spans more than one iteration
+constexpr int OFF_Q = 2 * T16;                    // QDO_STAGES stages
+constexpr int OFF_DO = 5 * T16;                   // QDO_STAGES stages
+constexpr int OFF_DS = 8 * T16;                   // 2 buffers x 32 KB ([kv][q] bf16, two 64-column sub-tiles each)
+constexpr int OFF_STG = 12 * T16;                 // 32 KB: fp32 dQ staging ([q][32 floats] x 2 sub-tiles)
+constexpr int OFF_STAT = 14 * T16;                // 2 buffers x {-lse*log2e [128], -delta*scale [128]} floats
+constexpr int OFF_BAR = OFF_STAT + 2 * 256 * 4;
+constexpr int SMEM_TOTAL = OFF_BAR + 256;
+static_assert(SMEM_TOTAL <= 232448, "shared memory budget");
+constexpr uint32_t TM_S = 0, TM_DP = 128, TM_DV = 256, TM_DK = 320, TM_DQ = 384, TM_P = 448;
 
 struct Bars {
-    uint64_t kv_full, qdo_full[2], qdo_empty[2], sdp_full, sdp_free, pds_ready, dq_full, dq_free;
+    uint64_t kv_full, qdo_full[QDO_STAGES], qdo_empty[QDO_STAGES], sdp_full, sdp_free, p_ready, p_free, ds_ready[2], ds_free[2], dq_full, dq_free;
     uint32_t tmem_ptr;
 };
+static_assert(sizeof(Bars) <= 256, "barrier block");
 
-
-// One 32-column chunk of a row: P = exp2(S*scale_log2 - lse_l2), dS = scale * P o (dP - delta) -> packed bf16 pairs.
+// One 32-column chunk of a key row: P^T = exp2(S^T*scale_log2 + nl[q]), dS^T = P^T o (dP^T*scale + nd[q]) -> packed bf16.
+// nl = -LSE*log2e (or -inf for query rows past the end), nd = -delta*scale; both broadcast from smem.
 template <bool MASK>
-__device__ __forceinline__ void pds_chunk(const uint32_t* sv, const uint32_t* dv, uint32_t* pk, uint32_t* dsk, float scale_log2,
-                                          float lse_l2, float dlt, float scale, int col0, int limit) {
-    const float2 sc2 = make_float2(scale_log2, scale_log2), nl2 = make_float2(-lse_l2, -lse_l2);
-    const float2 nd2 = make_float2(-dlt * scale, -dlt * scale), s2 = make_float2(scale, scale);
+__device__ __forceinline__ void pds_chunk(const uint32_t* sv, const uint32_t* dv, uint32_t* pk, uint32_t* dsk, const float* nl,
+                                          const float* nd, float scale_log2, float scale, int first_valid) {
+    const float2 sc2 = make_float2(scale_log2, scale_log2), s2 = make_float2(scale, scale);
 #pragma unroll
-    for (int i = 0; i < 32; i += 2) {
-        const float2 x = __ffma2_rn(make_float2(__uint_as_float(sv[i]), __uint_as_float(sv[i + 1])), sc2, nl2);
-        float2 p = make_float2(ex2(x.x), ex2(x.y));
-        if (MASK) {
-            if (col0 + i >= limit) p.x = 0.f;
-            if (col0 + i + 1 >= limit) p.y = 0.f;
+    for (int i = 0; i < 32; i += 4) {
+        const float4 l4 = *(const float4*)(nl + i), d4 = *(const float4*)(nd + i);
+        const float2 x0 = __ffma2_rn(make_float2(__uint_as_float(sv[i]), __uint_as_float(sv[i + 1])), sc2, make_float2(l4.x, l4.y));
+        const float2 x1 = __ffma2_rn(make_float2(__uint_as_float(sv[i + 2]), __uint_as_float(sv[i + 3])), sc2, make_float2(l4.z, l4.w));
+        float2 p0 = make_float2(ex2(x0.x), ex2(x0.y)), p1 = make_float2(ex2(x1.x), ex2(x1.y));
+        if (MASK) {               // causal: query column c is visible to this key row only if c >= first_valid
+            if (i < first_valid) p0.x = 0.f;
+            if (i + 1 < first_valid) p0.y = 0.f;
+            if (i + 2 < first_valid) p1.x = 0.f;
+            if (i + 3 < first_valid) p1.y = 0.f;
         }
-        const float2 t = __ffma2_rn(make_float2(__uint_as_float(dv[i]), __uint_as_float(dv[i + 1])), s2, nd2);   // scale*(dP - delta)
-        const float2 d = __fmul2_rn(p, t);
-        pk[i >> 1] = pack_bf16(p.x, p.y);
-        dsk[i >> 1] = pack_bf16(d.x, d.y);
+        const float2 t0 = __ffma2_rn(make_float2(__uint_as_float(dv[i]), __uint_as_float(dv[i + 1])), s2, make_float2(d4.x, d4.y));
+        const float2 t1 = __ffma2_rn(make_float2(__uint_as_float(dv[i + 2]), __uint_as_float(dv[i + 3])), s2, make_float2(d4.z, d4.w));
+        const float2 d0 = __fmul2_rn(p0, t0), d1 = __fmul2_rn(p1, t1);
+        pk[i >> 1] = pack_bf16(p0.x, p0.y); pk[(i >> 1) + 1] = pack_bf16(p1.x, p1.y);
+        dsk[i >> 1] = pack_bf16(d0.x, d0.y); dsk[(i >> 1) + 1] = pack_bf16(d1.x, d1.y);
     }
 }
 
@@ -58,8 +67,7 @@ __global__ void __launch_bounds__(NTHREADS, 1)
 attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
                 const __grid_constant__ CUtensorMap tmDQKV, const __grid_constant__ CUtensorMap tmDQ,
                 const float* __restrict__ lse, const float* __restrict__ delta, int S, int H, float scale, int causal) {
-    extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    extern __shared__ __align__(1024) uint8_t smem[];
     Bars* bars = (Bars*)(smem + OFF_BAR);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int jt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
@@ -69,23 +77,25 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
     const int kv0 = jt * TILE;
 
     if (threadIdx.x == 0) {
+        if (smem_u32(smem) & 1023u) { printf("avion_b200: attn_bwd dynamic smem base not 1024-byte aligned\n"); __trap(); }
         tma_prefetch_desc(&tmQKV); tma_prefetch_desc(&tmDO); tma_prefetch_desc(&tmDQKV); tma_prefetch_desc(&tmDQ);
         mbar_init(&bars->kv_full, 1);
-        for (int i = 0; i < 2; ++i) { mbar_init(&bars->qdo_full[i], 1); mbar_init(&bars->qdo_empty[i], 1); }
+        for (int i = 0; i < QDO_STAGES; ++i) { mbar_init(&bars->qdo_full[i], 1); mbar_init(&bars->qdo_empty[i], 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&bars->ds_ready[i], 256); mbar_init(&bars->ds_free[i], 1); }
         mbar_init(&bars->sdp_full, 1); mbar_init(&bars->sdp_free, 256);
-        mbar_init(&bars->pds_ready, 256); mbar_init(&bars->dq_full, 1); mbar_init(&bars->dq_free, 256);
+        mbar_init(&bars->p_ready, 256); mbar_init(&bars->p_free, 1);
+        mbar_init(&bars->dq_full, 1); mbar_init(&bars->dq_free, 128);
         fence_barrier_init();
     }
-    if (warp == 8) tmem_alloc(&bars->tmem_ptr, 512);
+    if (warp == 12) tmem_alloc(&bars->tmem_ptr, 512);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = bars->tmem_ptr;
 
-    // the 8 math warps take the registers of the control warpgroup (setmaxnreg is per warpgroup: warps 8-11 all shrink)
-    if (warp >= 10) {
-        reg_dec<40>();       // idle warps: only complete the third warpgroup
-    } else if (warp == 9) {
+    if (warp >= 14) {
+        reg_dec<40>();       // idle warps: only complete the fourth warpgroup
+    } else if (warp == 13) {
         // ===================== TMA producer =====================
         // (whole warp loops and waits; one elected lane issues, so addresses and coordinates stay in uniform registers)
         reg_dec<40>();
@@ -96,8 +106,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
         }
         __syncwarp();
         for (int t = 0; t < n_i; ++t) {
-            const int st = t & 1;
-            mbar_wait(&bars->qdo_empty[st], ((t >> 1) & 1) ^ 1);
+            const int st = t % QDO_STAGES;
+            mbar_wait(&bars->qdo_empty[st], ((t / QDO_STAGES) & 1) ^ 1);
             if (elect_one()) {
                 mbar_expect_tx(&bars->qdo_full[st], 2 * T16);
                 tma_load_3d(smem + OFF_Q + st * T16, &tmQKV, &bars->qdo_full[st], h * HD, (i0 + t) * TILE, b);
@@ -105,28 +115,28 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
             }
             __syncwarp();
         }
-    } else if (warp == 8) {
+    } else if (warp == 12) {
         // ===================== MMA issuer =====================
         // waits are executed by the whole warp, the MMAs by one elected lane (descriptors stay in uniform registers)
         reg_dec<40>();
         if (n_i > 0) {
             constexpr uint32_t idesc_s = umma_idesc_bf16(TILE, TILE, false, false);
-            constexpr uint32_t idesc_dkv = umma_idesc_bf16(TILE, HD, true, true);
-            constexpr uint32_t idesc_dq = umma_idesc_bf16(TILE, HD, false, true);
+            constexpr uint32_t idesc_kn = umma_idesc_bf16(TILE, HD, false, true);    // A K-major (or TMEM), B MN-major
+            constexpr uint32_t idesc_nn = umma_idesc_bf16(TILE, HD, true, true);     // A MN-major, B MN-major
             const uint32_t ka = smem_u32(smem + OFF_K), va = smem_u32(smem + OFF_V);
             auto issue_sdp = [&](int t) {
-                const int st = t & 1;
-                mbar_wait(&bars->qdo_full[st], (t >> 1) & 1);
+                const int st = t % QDO_STAGES;
+                mbar_wait(&bars->qdo_full[st], (t / QDO_STAGES) & 1);
                 if (t > 0) mbar_wait(&bars->sdp_free, (t - 1) & 1);
                 tc_fence_after();
                 if (elect_one()) {
                     const uint32_t qa = smem_u32(smem + OFF_Q + st * T16), doa = smem_u32(smem + OFF_DO + st * T16);
 #pragma unroll
-                    for (int k = 0; k < HD / 16; ++k)
-                        umma_ss(tmem_base + TM_S, umma_smem_desc(qa + k * 32, 16, 1024), umma_smem_desc(ka + k * 32, 16, 1024), idesc_s, k > 0);
+                    for (int k = 0; k < HD / 16; ++k)      // S^T = K Q^T
+                        umma_ss(tmem_base + TM_S, umma_smem_desc(ka + k * 32, 16, 1024), umma_smem_desc(qa + k * 32, 16, 1024), idesc_s, k > 0);
 #pragma unroll
-                    for (int k = 0; k < HD / 16; ++k)
-                        umma_ss(tmem_base + TM_DP, umma_smem_desc(doa + k * 32, 16, 1024), umma_smem_desc(va + k * 32, 16, 1024), idesc_s, k > 0);
+                    for (int k = 0; k < HD / 16; ++k)      // dP^T = V dO^T
+                        umma_ss(tmem_base + TM_DP, umma_smem_desc(va + k * 32, 16, 1024), umma_smem_desc(doa + k * 32, 16, 1024), idesc_s, k > 0);
                     umma_commit(&bars->sdp_full);
                 }
                 __syncwarp();
@@ -134,82 +144,115 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
             mbar_wait(&bars->kv_full, 0);
             issue_sdp(0);
             for (int t = 0; t < n_i; ++t) {
-                const int st = t & 1;
+                const int st = t % QDO_STAGES, db = t & 1;
                 if (t + 1 < n_i) issue_sdp(t + 1);
-                mbar_wait(&bars->pds_ready, t & 1);
-                tc_fence_after();
                 const uint32_t qa = smem_u32(smem + OFF_Q + st * T16), doa = smem_u32(smem + OFF_DO + st * T16);
-                const uint32_t pa = smem_u32(smem + OFF_P + st * 2 * T16), dsa = smem_u32(smem + OFF_DS + st * 2 * T16);
+                const uint32_t dsa = smem_u32(smem + OFF_DS + db * 2 * T16);
+                mbar_wait(&bars->p_ready, t & 1);
+                tc_fence_after();
                 if (elect_one()) {
 #pragma unroll
-                    for (int k = 0; k < TILE / 16; ++k)      // dV += P^T dO   (A = P as MN-major, B = dO as MN-major)
-                        umma_ss(tmem_base + TM_DV, umma_smem_desc(pa + k * 2048, 16384, 1024), umma_smem_desc(doa + k * 2048, 8192, 1024),
-                                idesc_dkv, (t > 0 || k > 0) ? 1u : 0u);
+                    for (int k = 0; k < TILE / 16; ++k)      // dV += P^T dO   (A = P^T from TMEM, 8 columns per K=16; B = dO MN-major)
+                        umma_ts(tmem_base + TM_DV, tmem_base + TM_P + k * 8, umma_smem_desc(doa + k * 2048, 8192, 1024),
+                                idesc_kn, (t > 0 || k > 0) ? 1u : 0u);
+                    umma_commit(&bars->p_free);
+                }
+                __syncwarp();
+                mbar_wait(&bars->ds_ready[db], (t >> 1) & 1);
+                tc_fence_after();
+                if (elect_one()) {
 #pragma unroll
-                    for (int k = 0; k < TILE / 16; ++k)      // dK += dS^T Q
-                        umma_ss(tmem_base + TM_DK, umma_smem_desc(dsa + k * 2048, 16384, 1024), umma_smem_desc(qa + k * 2048, 8192, 1024),
-                                idesc_dkv, (t > 0 || k > 0) ? 1u : 0u);
+                    for (int k = 0; k < TILE / 16; ++k)      // dK += dS^T Q   (A = dS^T K-major, B = Q MN-major)
+                        umma_ss(tmem_base + TM_DK, umma_smem_desc(dsa + (k >> 2) * 16384 + (k & 3) * 32, 16, 1024),
+                                umma_smem_desc(qa + k * 2048, 8192, 1024), idesc_kn, (t > 0 || k > 0) ? 1u : 0u);
+                    umma_commit(&bars->qdo_empty[st]);       // Q_t / dO_t are not read after dK
                 }
                 __syncwarp();
                 if (t > 0) { mbar_wait(&bars->dq_free, (t - 1) & 1); tc_fence_after(); }   // dQ_{t-1} has left TMEM
                 if (elect_one()) {
 #pragma unroll
-                    for (int k = 0; k < TILE / 16; ++k)      // dQ_i = dS K_j  (A = dS K-major, B = K_j as MN-major)
-                        umma_ss(tmem_base + TM_DQ, umma_smem_desc(dsa + (k >> 2) * 16384 + (k & 3) * 32, 16, 1024),
-                                umma_smem_desc(ka + k * 2048, 8192, 1024), idesc_dq, k > 0 ? 1u : 0u);
+                    for (int k = 0; k < TILE / 16; ++k)      // dQ_i = dS K_j  (A = dS^T bytes read MN-major, B = K_j MN-major)
+                        umma_ss(tmem_base + TM_DQ, umma_smem_desc(dsa + k * 2048, 16384, 1024),
+                                umma_smem_desc(ka + k * 2048, 8192, 1024), idesc_nn, k > 0 ? 1u : 0u);
                     umma_commit(&bars->dq_full);
-                    umma_commit(&bars->qdo_empty[st]);
+                    umma_commit(&bars->ds_free[db]);
                 }
                 __syncwarp();
             }
         }
+    } else if (warp >= 8) {
+        // ===================== dQ drain: TMEM -> fp32 staging -> TMA reduce-add =====================
+        reg_dec<88>();
+        const int row = (warp & 3) * 32 + lane;
+        const uint32_t lane_addr = (uint32_t)((warp & 3) * 32) << 16;
+        const bool leader = (threadIdx.x == 256);
+        for (int t = 0; t < n_i; ++t) {
+            mbar_wait(&bars->dq_full, t & 1);
+            tc_fence_after();
+            uint32_t v[64];
+            tmem_ld32(tmem_base + lane_addr + TM_DQ, v);
+            tmem_ld32(tmem_base + lane_addr + TM_DQ + 32, v + 32);
+            tmem_ld_wait();
+            tc_fence_before();
+            mbar_arrive(&bars->dq_free);
+            uint8_t* stg = smem + OFF_STG;
+            if (t >= 1) {                            // the reduce of tile t-1 must have finished reading the staging tile
+                if (leader) tma_wait_group_read0();
+                named_bar_sync(2, 128);
+            }
+#pragma unroll
+            for (int c = 0; c < 2; ++c)
+#pragma unroll
+                for (int i = 0; i < 8; ++i)
+                    st_shared_v4(stg + c * T16 + row * 128 + ((i ^ (row & 7)) << 4),
+                                 make_uint4(v[c * 32 + 4 * i], v[c * 32 + 4 * i + 1], v[c * 32 + 4 * i + 2], v[c * 32 + 4 * i + 3]));
+            fence_proxy_async_smem();
+            named_bar_sync(2, 128);
+            if (leader) {
+                tma_reduce_add_3d(&tmDQ, stg, h * HD, (i0 + t) * TILE, b);
+                tma_reduce_add_3d(&tmDQ, stg + T16, h * HD + 32, (i0 + t) * TILE, b);
+                tma_commit_group();
+            }
+        }
+        if (leader) tma_wait_group0();
     } else {
-        // ===================== compute warps: thread = (row, column half) =====================
-        reg_inc<232>();
+        // ===================== compute warps: thread = (key row, half of the query columns) =====================
+        reg_inc<192>();
         if (n_i > 0) {
         const int half = warp >> 2;
         const int row = (warp & 3) * 32 + lane;
         const uint32_t lane_addr = (uint32_t)((warp & 3) * 32) << 16;
         const float scale_log2 = scale * 1.4426950408889634f;
-        const bool leader = (threadIdx.x & 127) == 0;
         const long long stat_base = ((long long)b * H + h) * S;
-
-        // partial dQ of query tile t: TMEM -> fp32 staging (the P buffer of tile t, free now) -> TMA reduce-add
-        auto drain_dq = [&](int t) {
-            mbar_wait(&bars->dq_full, t & 1);      // all MMAs of tile t are complete
-            tc_fence_after();
-            uint32_t v[32];
-            tmem_ld32(tmem_base + lane_addr + TM_DQ + half * 32, v);
-            tmem_ld_wait();
-            tc_fence_before();
-            mbar_arrive(&bars->dq_free);
-            uint8_t* stg = smem + OFF_P + (t & 1) * 2 * T16 + half * T16;
-#pragma unroll
-            for (int i = 0; i < 8; ++i)
-                st_shared_v4(stg + row * 128 + ((i ^ (row & 7)) << 4), make_uint4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]));
-            fence_proxy_async_smem();
-            named_bar_sync(1 + half, 128);
-            if (leader) { tma_reduce_add_3d(&tmDQ, stg, h * HD + half * 32, (i0 + t) * TILE, b); tma_commit_group(); }
+        float* stat = (float*)(smem + OFF_STAT);
+        // per-query-row statistics of tile t live in stat[(t&1)*256 ...]: threads 0-127 own -lse*log2e, 128-255 own -delta*scale
+        const int sidx = threadIdx.x & 127;
+        const bool own_lse = threadIdx.x < 128;
+        // the raw global value is kept in a register for a whole tile and only converted when it is stored: the use of
+        // a load result is what stalls, so the conversion must not sit right behind the load
+        const float* stat_src = (own_lse ? lse : delta) + stat_base;
+        const float stat_mul = own_lse ? -1.4426950408889634f : -scale;
+        auto load_stat = [&](int t) -> float {
+            const int qr = (i0 + t) * TILE + sidx;
+            return qr < S ? __ldg(stat_src + qr) : (own_lse ? INFINITY : 0.f);      // -inf after scaling: P = 0 past the end
         };
+        stat[threadIdx.x] = load_stat(0) * stat_mul;
+        float stat_nx = n_i > 1 ? load_stat(1) : 0.f;
 
-        float lse_nx = 0.f, dlt_nx = 0.f;
-        { const int qr = i0 * TILE + row; if (qr < S) { lse_nx = __ldg(lse + stat_base + qr); dlt_nx = __ldg(delta + stat_base + qr); } }
         for (int t = 0; t < n_i; ++t) {
+            const int buf = t & 1;
             const int q0 = (i0 + t) * TILE;
-            const int qrow = q0 + row;
-            const bool row_ok = qrow < S;
-            const float lse_l2 = lse_nx * 1.4426950408889634f, dlt = dlt_nx;
-            if (t + 1 < n_i) {                      // prefetch the next tile's row statistics
-                const int qr = qrow + TILE;
-                lse_nx = 0.f; dlt_nx = 0.f;
-                if (qr < S) { lse_nx = __ldg(lse + stat_base + qr); dlt_nx = __ldg(delta + stat_base + qr); }
-            }
-            // valid columns of this thread's row: [0, limit) in tile coordinates
-            const int limit = row_ok ? (causal ? min(S - kv0, qrow - kv0 + 1) : (S - kv0)) : 0;
-            const bool need_mask = (kv0 + TILE > S) || (q0 + TILE > S) || (causal && kv0 + TILE - 1 > q0);   // warp-uniform
+            const bool need_mask = causal && (q0 < kv0 + TILE - 1);      // diagonal tile of the causal text tower (warp-uniform)
             mbar_wait(&bars->sdp_full, t & 1);
             tc_fence_after();
-            uint32_t pk[32], dsk[32];     // packed bf16: 64 P values and 64 dS values of this thread
+            named_bar_sync(1, 256);           // stat[buf] is complete; nobody still reads stat[buf^1] (tile t-1)
+            if (t + 1 < n_i) {
+                stat[(buf ^ 1) * 256 + threadIdx.x] = stat_nx * stat_mul;
+                if (t + 2 < n_i) stat_nx = load_stat(t + 2);
+            }
+            const float* nl = stat + buf * 256 + half * 64;
+            const float* nd = nl + 128;
+            uint32_t pk[32], dsk[32];     // packed bf16: 64 P^T values and 64 dS^T values of this thread
 #pragma unroll
             for (int c = 0; c < 2; ++c) {
                 uint32_t sv[32], dv[32];
@@ -217,29 +260,31 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
                 tmem_ld32(tmem_base + lane_addr + TM_DP + half * 64 + c * 32, dv);
                 tmem_ld_wait();
                 if (c == 1) { tc_fence_before(); mbar_arrive(&bars->sdp_free); }
-                if (need_mask) pds_chunk<true>(sv, dv, pk + c * 16, dsk + c * 16, scale_log2, lse_l2, dlt, scale, half * 64 + c * 32, limit);
-                else pds_chunk<false>(sv, dv, pk + c * 16, dsk + c * 16, scale_log2, lse_l2, dlt, scale, half * 64 + c * 32, limit);
+                // causal: key kv0+row is visible to query q0+col iff col >= kv0 + row - q0
+                const int first_valid = kv0 + row - q0 - (half * 64 + c * 32);
+                if (need_mask) pds_chunk<true>(sv, dv, pk + c * 16, dsk + c * 16, nl + c * 32, nd + c * 32, scale_log2, scale, first_valid);
+                else pds_chunk<false>(sv, dv, pk + c * 16, dsk + c * 16, nl + c * 32, nd + c * 32, scale_log2, scale, 0);
             }
-            // buffer t&1 last held P/dS of tile t-2 (its MMAs completed before drain_dq(t-2) returned) and, in its P half,
-            // the staging tile of dQ_{t-2}: the TMA reduce must have finished reading it
-            if (t >= 2) {
-                if (leader) tma_wait_group_read0();
-                named_bar_sync(1 + half, 128);
-            }
-            uint8_t* prow = smem + OFF_P + (t & 1) * 2 * T16 + half * T16 + row * 128;
-            uint8_t* drow = smem + OFF_DS + (t & 1) * 2 * T16 + half * T16 + row * 128;
+            // dS^T -> smem [kv][q]: buffer t&1 was last read by the dK/dQ MMAs of tile t-2.  The stores are issued first and
+            // complete while P^T goes to TMEM.
+            if (t >= 2) mbar_wait(&bars->ds_free[buf], ((t >> 1) - 1) & 1);
+            uint8_t* drow = smem + OFF_DS + buf * 2 * T16 + half * T16 + row * 128;
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const int off = (i ^ (row & 7)) << 4;
-                st_shared_v4(prow + off, make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]));
-                st_shared_v4(drow + off, make_uint4(dsk[4 * i], dsk[4 * i + 1], dsk[4 * i + 2], dsk[4 * i + 3]));
-            }
+            for (int i = 0; i < 8; ++i)
+                st_shared_v4(drow + ((i ^ (row & 7)) << 4), make_uint4(dsk[4 * i], dsk[4 * i + 1], dsk[4 * i + 2], dsk[4 * i + 3]));
+            // P^T -> TMEM (bf16 pairs, lane = key row): dV_{t-1} must have finished reading the previous P^T
+            if (t > 0) { mbar_wait(&bars->p_free, (t - 1) & 1); tc_fence_after(); }
+            tmem_st32(tmem_base + lane_addr + TM_P + half * 32, pk);
+            tmem_st_wait();
+            tc_fence_before();
+            mbar_arrive(&bars->p_ready);
             fence_proxy_async_smem();
-            mbar_arrive(&bars->pds_ready);
-            if (t > 0) drain_dq(t - 1);            // overlaps the MMAs of tile t
+            mbar_arrive(&bars->ds_ready[buf]);
         }
-        drain_dq(n_i - 1);      // also guarantees that dV and dK are complete
-        // dV, dK: TMEM -> bf16 -> swizzled smem (the dS buffers are free now and never touched by the dQ reduces) -> TMA store
+        // every MMA has completed once the last ds_free fires (it is committed after dQ of the last tile)
+        mbar_wait(&bars->ds_free[(n_i - 1) & 1], ((n_i - 1) >> 1) & 1);
+        tc_fence_after();
+        // dV, dK: TMEM -> bf16 -> swizzled smem (the dS buffers are free now) -> TMA store
         {
             uint32_t v[32], k[32];
             tmem_ld32(tmem_base + lane_addr + TM_DV + half * 32, v);
@@ -252,28 +297,28 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
             for (int i = 0; i < 4; ++i) {
                 const int off = ((half * 4 + i) ^ (row & 7)) << 4;
                 st_shared_v4(vrow + off, make_uint4(pack_bf16(__uint_as_float(v[8 * i]), __uint_as_float(v[8 * i + 1])),
-                                                   pack_bf16(__uint_as_float(v[8 * i + 2]), __uint_as_float(v[8 * i + 3])),
-                                                   pack_bf16(__uint_as_float(v[8 * i + 4]), __uint_as_float(v[8 * i + 5])),
-                                                   pack_bf16(__uint_as_float(v[8 * i + 6]), __uint_as_float(v[8 * i + 7]))));
+                                                    pack_bf16(__uint_as_float(v[8 * i + 2]), __uint_as_float(v[8 * i + 3])),
+                                                    pack_bf16(__uint_as_float(v[8 * i + 4]), __uint_as_float(v[8 * i + 5])),
+                                                    pack_bf16(__uint_as_float(v[8 * i + 6]), __uint_as_float(v[8 * i + 7]))));
                 st_shared_v4(krow + off, make_uint4(pack_bf16(__uint_as_float(k[8 * i]), __uint_as_float(k[8 * i + 1])),
-                                                   pack_bf16(__uint_as_float(k[8 * i + 2]), __uint_as_float(k[8 * i + 3])),
-                                                   pack_bf16(__uint_as_float(k[8 * i + 4]), __uint_as_float(k[8 * i + 5])),
-                                                   pack_bf16(__uint_as_float(k[8 * i + 6]), __uint_as_float(k[8 * i + 7]))));
+                                                    pack_bf16(__uint_as_float(k[8 * i + 2]), __uint_as_float(k[8 * i + 3])),
+                                                    pack_bf16(__uint_as_float(k[8 * i + 4]), __uint_as_float(k[8 * i + 5])),
+                                                    pack_bf16(__uint_as_float(k[8 * i + 6]), __uint_as_float(k[8 * i + 7]))));
             }
             fence_proxy_async_smem();
-            named_bar_sync(3, 256);
+            named_bar_sync(1, 256);
             if (threadIdx.x == 0) {
                 tma_store_3d(&tmDQKV, smem + OFF_DS + 2 * T16, (H + h) * HD, kv0, b);
                 tma_store_3d(&tmDQKV, smem + OFF_DS, (2 * H + h) * HD, kv0, b);
                 tma_commit_group();
+                tma_wait_group0();
             }
-            if (leader) tma_wait_group0();
         }
         }   // n_i > 0
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 8) tmem_dealloc(tmem_base, 512);
+    if (warp == 12) tmem_dealloc(tmem_base, 512);
 }
 
 // delta[b][h][s] = sum_d dO[b][s][h][d] * O[b][s][h][d]
