@@ -92,6 +92,10 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 
+__device__ __forceinline__ void named_bar_arrive(int id, int nthreads) {
+    asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
 // ---- TMA ------------------------------------------------------------------------------------------------------
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* m) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(m) : "memory");
@@ -286,6 +290,32 @@ __device__ __forceinline__ float gelu_erf_grad(float x) {
     const float q = gelu_tail(x, e);
     const float cdf = x >= 0.f ? 1.0f - q : q;
     return fmaf(x * 0.3989422804014327f, e, cdf);
+}
+
+// Packed (two elements per instruction: FFMA2/FMUL2) forms of the same arithmetic; bit-identical to the scalar versions.
+__device__ __forceinline__ float2 gelu_tail2(float2 x, float2 nax, float2& e) {
+    const float2 d = __ffma2_rn(nax, make_float2(-0.3275911f * 0.70710678118654752f, -0.3275911f * 0.70710678118654752f), make_float2(1.0f, 1.0f));
+    const float2 t = make_float2(rcp_approx(d.x), rcp_approx(d.y));
+    const float2 a = __fmul2_rn(__fmul2_rn(x, x), make_float2(-0.72134752044448170f, -0.72134752044448170f));
+    e = make_float2(ex2(a.x), ex2(a.y));
+    float2 p = __ffma2_rn(make_float2(0.5f * 1.061405429f, 0.5f * 1.061405429f), t, make_float2(0.5f * -1.453152027f, 0.5f * -1.453152027f));
+    p = __ffma2_rn(p, t, make_float2(0.5f * 1.421413741f, 0.5f * 1.421413741f));
+    p = __ffma2_rn(p, t, make_float2(0.5f * -0.284496736f, 0.5f * -0.284496736f));
+    p = __ffma2_rn(p, t, make_float2(0.5f * 0.254829592f, 0.5f * 0.254829592f));
+    return __fmul2_rn(__fmul2_rn(p, t), e);
+}
+__device__ __forceinline__ float2 gelu_erf2(float2 x) {
+    float2 e;
+    const float2 nax = make_float2(-fabsf(x.x), -fabsf(x.y));
+    const float2 q = gelu_tail2(x, nax, e);
+    return __ffma2_rn(nax, q, make_float2(fmaxf(x.x, 0.f), fmaxf(x.y, 0.f)));
+}
+__device__ __forceinline__ float2 gelu_erf_grad2(float2 x) {
+    float2 e;
+    const float2 nax = make_float2(-fabsf(x.x), -fabsf(x.y));
+    const float2 q = gelu_tail2(x, nax, e);
+    const float2 cdf = make_float2(x.x >= 0.f ? 1.0f - q.x : q.x, x.y >= 0.f ? 1.0f - q.y : q.y);
+    return __ffma2_rn(__fmul2_rn(x, make_float2(0.3989422804014327f, 0.3989422804014327f)), e, cdf);
 }
 
 __device__ __forceinline__ float warp_sum(float v) {

@@ -199,7 +199,12 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                     for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
                     if (EPI == AVN_EPI_BIAS || EPI == AVN_EPI_BIAS_GELU || EPI == AVN_EPI_BIAS_GELU_DUAL || EPI == AVN_EPI_BIAS_RESIDUAL) {
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) f[j] += bias_s[u * 32 + j];
+                        for (int j = 0; j < 32; j += 4) {
+                            const float4 b4 = *(const float4*)(bias_s + u * 32 + j);
+                            const float2 r0 = __fadd2_rn(make_float2(f[j], f[j + 1]), make_float2(b4.x, b4.y));
+                            const float2 r1 = __fadd2_rn(make_float2(f[j + 2], f[j + 3]), make_float2(b4.z, b4.w));
+                            f[j] = r0.x; f[j + 1] = r0.y; f[j + 2] = r1.x; f[j + 3] = r1.y;
+                        }
                     }
                     if (EPI == AVN_EPI_BIAS_RESIDUAL || EPI == AVN_EPI_DGELU) {
                         const __nv_bfloat16* rp = p.R + (long long)mb * p.r_batch_stride + (long long)m * p.ldr + nc;
@@ -210,9 +215,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                             const uint32_t rr[4] = {rv.x, rv.y, rv.z, rv.w};
 #pragma unroll
                             for (int e = 0; e < 4; ++e) {
-                                float2 x = unpack_bf16(rr[e]);
-                                if (EPI == AVN_EPI_BIAS_RESIDUAL) { f[8 * i + 2 * e] += x.x; f[8 * i + 2 * e + 1] += x.y; }
-                                else { f[8 * i + 2 * e] *= gelu_erf_grad(x.x); f[8 * i + 2 * e + 1] *= gelu_erf_grad(x.y); }
+                                const float2 x = unpack_bf16(rr[e]);
+                                const float2 cur = make_float2(f[8 * i + 2 * e], f[8 * i + 2 * e + 1]);
+                                const float2 r = (EPI == AVN_EPI_BIAS_RESIDUAL) ? __fadd2_rn(cur, x) : __fmul2_rn(cur, gelu_erf_grad2(x));
+                                f[8 * i + 2 * e] = r.x; f[8 * i + 2 * e + 1] = r.y;
                             }
                         }
                     }
@@ -222,7 +228,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                     }
                     if (EPI == AVN_EPI_BIAS_GELU || EPI == AVN_EPI_BIAS_GELU_DUAL) {
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) f[j] = gelu_erf(f[j]);
+                        for (int j = 0; j < 32; j += 2) {
+                            const float2 g = gelu_erf2(make_float2(f[j], f[j + 1]));
+                            f[j] = g.x; f[j + 1] = g.y;
+                        }
                     }
                     if ((u & 1) == 0) {         // starting a new 64-column staging tile
                         if (gtid == 0) tma_wait_group_read0();
