@@ -8,13 +8,14 @@
 //   NN: A K-major, B MN-major       (dgrad:    dY[M,N'] * W[N',K'])
 //   TN: A MN-major, B MN-major      (wgrad:    dY[tok,N]^T * X[tok,K], contraction over tokens, split-K)
 // Replaces the cuBLAS calls behind nn.Linear / FlashMHA / FlashMlp in avion/models/transformer.py:116-120,135,227,320.
+#include <stdlib.h>
 #include "common.cuh"
 #include "../../include/avion_b200.h"
 
 namespace {
 using namespace avn;
 
-constexpr int BM = 128, BK = 64, STAGES = 4;
+constexpr int BM = 128, BK = 64;
 constexpr int EPI_WARPS = 8;
 constexpr int NTHREADS = 64 + EPI_WARPS * 32;
 constexpr int A_STAGE_BYTES = BM * BK * 2;       // 16 KB
@@ -28,9 +29,13 @@ struct KParams {
     long long ldr, r_batch_stride;
 };
 
-template <int BN>
+// CG = CTAs per MMA (cta_group): with CG = 2 a CTA pair computes a 256 x BN tile, each CTA staging its own 128 rows of A and
+// HALF of the B tile - the tensor core's shared-memory operand reads, which bound the single-CTA kernel at about two
+// thirds of the MMA rate, drop from 96 to 64 bytes per clock per SM.
+template <int BN, int CG>
 struct Smem {
-    static constexpr int B_STAGE_BYTES = BN * BK * 2;
+    static constexpr int STAGES = (CG == 2) ? 6 : 4;
+    static constexpr int B_STAGE_BYTES = (BN / CG) * BK * 2;
     static constexpr int OFF_A = 0;
     static constexpr int OFF_B = OFF_A + STAGES * A_STAGE_BYTES;
     static constexpr int OFF_STG = OFF_B + STAGES * B_STAGE_BYTES;
@@ -39,13 +44,14 @@ struct Smem {
     static constexpr int TOTAL = OFF_BAR + 256 + 1024;   // + alignment slack
 };
 
-template <int BN, int MODE, int EPI>
+template <int BN, int MODE, int EPI, int CG>
 __global__ void __launch_bounds__(NTHREADS, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
             const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmC2, const KParams p) {
     constexpr bool A_MN = (MODE == AVN_GEMM_TN);
     constexpr bool B_MN = (MODE != AVN_GEMM_NT);
-    using L = Smem<BN>;
+    using L = Smem<BN, CG>;
+    constexpr int STAGES = L::STAGES;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     uint8_t* sA = smem + L::OFF_A;
@@ -59,51 +65,59 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     uint32_t* tmem_ptr = (uint32_t*)(tempty_bar + 2);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int rank = (CG == 2) ? (int)cluster_ctarank() : 0;      // position inside the CTA pair; rank 0 issues the MMAs
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmA);
         tma_prefetch_desc(&tmB);
         tma_prefetch_desc(&tmC);
         for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
-        for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], EPI_WARPS); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], EPI_WARPS * CG); }
         fence_barrier_init();
     }
-    if (warp == 1) tmem_alloc(tmem_ptr, 2 * BN);
+    if (warp == 1) { if (CG == 2) tmem_alloc_2cta(tmem_ptr, 2 * BN); else tmem_alloc(tmem_ptr, 2 * BN); }
     tc_fence_before();
-    __syncthreads();
+    if (CG == 2) cluster_sync_all(); else __syncthreads();      // the peer's barriers must exist before anything signals them
     tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr;
 
-    const int total_tiles = (MODE == AVN_GEMM_TN ? p.splits : p.batch) * p.m_tiles * p.n_tiles;
+    // tiles are enumerated per CTA pair: a unit covers CG * 128 rows, CTA `rank` owns rows (unit * CG + rank) * 128 ..
+    const int m_units = (p.m_tiles + CG - 1) / CG;
+    const int total_tiles = (MODE == AVN_GEMM_TN ? p.splits : p.batch) * m_units * p.n_tiles;
+    const int tile0 = blockIdx.x / CG, tile_step = gridDim.x / CG;
 
     if (warp == 0) {
         // ===================== TMA producer =====================
         if (lane == 0) {
             int stage = 0; uint32_t phase = 0;
-            for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+            for (int t = tile0; t < total_tiles; t += tile_step) {
                 int n_blk = t % p.n_tiles; int r = t / p.n_tiles;
-                int m_blk = r % p.m_tiles; int outer = r / p.m_tiles;       // batch (NT/NN) or split (TN)
+                int m_blk = (r % m_units) * CG + rank; int outer = r / m_units;       // batch (NT/NN) or split (TN)
                 int kb0 = 0, kb1 = p.kblocks;
                 if (MODE == AVN_GEMM_TN) { kb0 = outer * p.kb_per_split; kb1 = min(p.total_kb, kb0 + p.kb_per_split); }
-                const int m0 = m_blk * BM, n0 = n_blk * BN;
+                const int m0 = m_blk * BM, n0 = n_blk * BN + rank * (BN / CG);      // this CTA's rows of A and of B
+                auto load = [&](void* dst, const CUtensorMap* tm, uint64_t* bar, int c0, int c1, int c2) {
+                    if (CG == 2) tma_load_3d_2cta(dst, tm, bar, c0, c1, c2); else tma_load_3d(dst, tm, bar, c0, c1, c2);
+                };
                 for (int kb = kb0; kb < kb1; ++kb) {
                     mbar_wait(&empty_bar[stage], phase ^ 1);
                     uint8_t* a = sA + stage * A_STAGE_BYTES;
                     uint8_t* b = sB + stage * L::B_STAGE_BYTES;
-                    mbar_expect_tx(&full_bar[stage], A_STAGE_BYTES + L::B_STAGE_BYTES);
+                    // the leader's barrier counts the bytes of both CTAs (the peer's loads signal it, too)
+                    if (rank == 0) mbar_expect_tx(&full_bar[stage], CG * (A_STAGE_BYTES + L::B_STAGE_BYTES));
                     if (MODE == AVN_GEMM_TN) {
                         int kbatch = kb / p.kblocks, krow = (kb % p.kblocks) * BK;
 #pragma unroll
-                        for (int j = 0; j < BM / 64; ++j) tma_load_3d(a + j * 8192, &tmA, &full_bar[stage], m0 + 64 * j, krow, kbatch);
+                        for (int j = 0; j < BM / 64; ++j) load(a + j * 8192, &tmA, &full_bar[stage], m0 + 64 * j, krow, kbatch);
 #pragma unroll
-                        for (int j = 0; j < BN / 64; ++j) tma_load_3d(b + j * 8192, &tmB, &full_bar[stage], n0 + 64 * j, krow, kbatch);
+                        for (int j = 0; j < BN / CG / 64; ++j) load(b + j * 8192, &tmB, &full_bar[stage], n0 + 64 * j, krow, kbatch);
                     } else {
-                        tma_load_3d(a, &tmA, &full_bar[stage], kb * BK, m0, outer);
+                        load(a, &tmA, &full_bar[stage], kb * BK, m0, outer);
                         if (MODE == AVN_GEMM_NT) {
-                            tma_load_3d(b, &tmB, &full_bar[stage], kb * BK, n0, 0);
+                            load(b, &tmB, &full_bar[stage], kb * BK, n0, 0);
                         } else {
 #pragma unroll
-                            for (int j = 0; j < BN / 64; ++j) tma_load_3d(b + j * 8192, &tmB, &full_bar[stage], n0 + 64 * j, kb * BK, 0);
+                            for (int j = 0; j < BN / CG / 64; ++j) load(b + j * 8192, &tmB, &full_bar[stage], n0 + 64 * j, kb * BK, 0);
                         }
                     }
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -111,14 +125,15 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             }
         }
     } else if (warp == 1) {
-        // ===================== MMA issuer =====================
-        constexpr uint32_t idesc = umma_idesc_bf16(BM, BN, A_MN, B_MN);
+        // ===================== MMA issuer (leader CTA only) =====================
+        if (rank == 0) {
+        constexpr uint32_t idesc = umma_idesc_bf16(BM * CG, BN, A_MN, B_MN);
         constexpr uint32_t a_lbo = A_MN ? 8192 : 16, b_lbo = B_MN ? 8192 : 16;
         constexpr uint32_t a_adv = A_MN ? 2048 : 32, b_adv = B_MN ? 2048 : 32;    // bytes per UMMA_K = 16
         int stage = 0; uint32_t phase = 0;
         int acc = 0; uint32_t acc_phase = 0;
-        for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-            int outer = (t / p.n_tiles) / p.m_tiles;
+        for (int t = tile0; t < total_tiles; t += tile_step) {
+            int outer = (t / p.n_tiles) / m_units;
             int kb0 = 0, kb1 = p.kblocks;
             if (MODE == AVN_GEMM_TN) { kb0 = outer * p.kb_per_split; kb1 = min(p.total_kb, kb0 + p.kb_per_split); }
             mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
@@ -134,16 +149,23 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                     for (int k = 0; k < BK / 16; ++k) {
                         uint64_t ad = umma_smem_desc(a_addr + k * a_adv, a_lbo, 1024);
                         uint64_t bd = umma_smem_desc(b_addr + k * b_adv, b_lbo, 1024);
-                        umma_ss(d_tmem, ad, bd, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+                        if (CG == 2) umma_ss_2cta(d_tmem, ad, bd, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+                        else umma_ss(d_tmem, ad, bd, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
                     }
-                    umma_commit(&empty_bar[stage]);
-                    if (kb == kb1 - 1) umma_commit(&tfull_bar[acc]);
+                    if (CG == 2) {       // both CTAs' producers / epilogues are released
+                        umma_commit_2cta(&empty_bar[stage]);
+                        if (kb == kb1 - 1) umma_commit_2cta(&tfull_bar[acc]);
+                    } else {
+                        umma_commit(&empty_bar[stage]);
+                        if (kb == kb1 - 1) umma_commit(&tfull_bar[acc]);
+                    }
                 }
                 __syncwarp();
                 if (++stage == STAGES) { stage = 0; phase ^= 1; }
             }
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
+        }   // rank == 0
     } else {
         // ===================== epilogue =====================
         const int ew = warp - 2;
@@ -156,9 +178,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         float* bias_s = sBias + g * (BN / 2);
         constexpr int UNITS = BN / 2 / 32;      // 32-column units per group
         int acc = 0; uint32_t acc_phase = 0;
-        for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        for (int t = tile0; t < total_tiles; t += tile_step) {
             int n_blk = t % p.n_tiles; int r = t / p.n_tiles;
-            int m_blk = r % p.m_tiles; int outer = r / p.m_tiles;
+            int m_blk = (r % m_units) * CG + rank; int outer = r / m_units;
             const int mb = (MODE == AVN_GEMM_TN) ? 0 : outer;
             const int m0 = m_blk * BM, n0 = n_blk * BN + g * (BN / 2);
             const int m = m0 + row;
@@ -179,7 +201,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                 if (u == UNITS - 1) {           // accumulator fully read: hand the TMEM buffer back to the MMA warp
                     tc_fence_before();
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+                    if (lane == 0) { if (CG == 2) mbar_arrive_leader(&tempty_bar[acc]); else mbar_arrive(&tempty_bar[acc]); }
                 }
                 const int nc = n0 + u * 32;     // first global column of this unit
                 if (EPI == AVN_EPI_F32_ADD) {
@@ -268,13 +290,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         if (gtid == 0) tma_wait_group0();
     }
     tc_fence_before();
-    __syncthreads();
-    if (warp == 1) tmem_dealloc(tmem_base, 2 * BN);
+    if (CG == 2) cluster_sync_all(); else __syncthreads();      // neither CTA may leave while its peer can still signal it
+    if (warp == 1) { if (CG == 2) tmem_dealloc_2cta(tmem_base, 2 * BN); else tmem_dealloc(tmem_base, 2 * BN); }
 }
 
-template <int BN, int MODE, int EPI>
+template <int BN, int MODE, int EPI, int CG>
 int launch(const avn_gemm_desc* d, cudaStream_t stream) {
-    using L = Smem<BN>;
+    using L = Smem<BN, CG>;
     CUtensorMap tmA, tmB, tmC, tmC2;
     const bool tn = (MODE == AVN_GEMM_TN);
     int rc;
@@ -294,7 +316,7 @@ int launch(const avn_gemm_desc* d, cudaStream_t stream) {
     if (MODE == AVN_GEMM_NT) {
         uint64_t dims[3] = {(uint64_t)d->K, (uint64_t)d->N, 1};
         uint64_t str[2] = {(uint64_t)d->ldb * 2, (uint64_t)d->ldb * 2 * (uint64_t)d->N};
-        uint32_t box[3] = {64, (uint32_t)BN, 1};
+        uint32_t box[3] = {64, (uint32_t)(BN / CG), 1};
         if ((rc = avn_make_tmap(&tmB, d->B, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, 3, dims, str, box, true))) return rc;
     } else {
         const int bb = tn ? d->batch : 1;
@@ -326,19 +348,40 @@ int launch(const avn_gemm_desc* d, cudaStream_t stream) {
     p.n_tiles = (d->N + BN - 1) / BN;
     p.kblocks = (d->K + BK - 1) / BK;
     p.total_kb = p.kblocks * d->batch;
-    int splits = tn ? (d->splits > 0 ? d->splits : 1) : 1;
+    int splits = 1;
+    if (tn) {
+        splits = d->splits;
+        if (splits <= 0) {
+            // auto: the smallest split count (<= 16) whose tiles fill whole waves of CTAs (or CTA pairs) to >= 95 %, else the best one
+            const int units = ((p.m_tiles + CG - 1) / CG) * p.n_tiles, slots = avn_num_sms() / CG;
+            double best = 0.0;
+            splits = 1;
+            for (int sp = 1; sp <= 16; ++sp) {
+                const int tiles = units * sp, waves = (tiles + slots - 1) / slots;
+                const double eff = (double)tiles / ((double)waves * slots);
+                if (eff > best + 1e-9) { best = eff; splits = sp; }
+                if (eff >= 0.95) { splits = sp; break; }
+            }
+        }
+    }
     if (splits > p.total_kb) splits = p.total_kb;
     p.kb_per_split = (p.total_kb + splits - 1) / splits;
     p.splits = (p.total_kb + p.kb_per_split - 1) / p.kb_per_split;
     p.bias = d->bias;
     p.R = (const __nv_bfloat16*)d->R; p.ldr = d->ldr; p.r_batch_stride = d->r_batch_stride;
-    const int total_tiles = (tn ? p.splits : d->batch) * p.m_tiles * p.n_tiles;
-    int grid = avn_num_sms();
+    const int total_tiles = (tn ? p.splits : d->batch) * ((p.m_tiles + CG - 1) / CG) * p.n_tiles;
+    int grid = avn_num_sms() / CG;          // CTA pairs (or CTAs)
     if (grid > total_tiles) grid = total_tiles;
-    auto kern = gemm_kernel<BN, MODE, EPI>;
+    grid *= CG;
+    auto kern = gemm_kernel<BN, MODE, EPI, CG>;
     AVN_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
-    kern<<<grid, NTHREADS, L::TOTAL, stream>>>(tmA, tmB, tmC, tmC2, p);
-    AVN_CHECK_CUDA(cudaGetLastError());
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(NTHREADS); cfg.dynamicSmemBytes = L::TOTAL; cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = CG; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    AVN_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmC, tmC2, p));
     return AVN_OK;
 }
 
@@ -346,8 +389,14 @@ template <int MODE, int EPI>
 int launch_bn(const avn_gemm_desc* d, cudaStream_t stream) {
     // 256-wide tiles when N fills them and there are enough tiles to occupy the SMs; else 128-wide.
     const long long tiles256 = (long long)((d->M + 127) / 128) * ((d->N + 255) / 256) * (MODE == AVN_GEMM_TN ? 1 : d->batch);
-    if (d->N % 256 == 0 && (tiles256 >= 2 * avn_num_sms() || MODE == AVN_GEMM_TN)) return launch<256, MODE, EPI>(d, stream);
-    return launch<128, MODE, EPI>(d, stream);
+    // big problems: CTA pairs (cta_group::2) on 256 x 256 tiles; AVN_GEMM_CG=1 forces the single-CTA kernel (A/B comparisons)
+    static const int force_cg = getenv("AVN_GEMM_CG") ? atoi(getenv("AVN_GEMM_CG")) : 0;
+    if (d->N % 256 == 0 && (tiles256 >= 2 * avn_num_sms() || MODE == AVN_GEMM_TN)) {
+        const bool pair_ok = (MODE == AVN_GEMM_TN) ? (d->M % 256 == 0) : (tiles256 >= 4 * avn_num_sms());
+        if (force_cg != 1 && pair_ok) return launch<256, MODE, EPI, 2>(d, stream);
+        return launch<256, MODE, EPI, 1>(d, stream);
+    }
+    return launch<128, MODE, EPI, 1>(d, stream);
 }
 }  // namespace
 

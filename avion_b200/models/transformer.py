@@ -175,7 +175,7 @@ class _VisionTowerFn(torch.autograd.Function):
         dx_raw = ops.layernorm_bwd(g, x_raw, lnpre_w.detach(), mpre, rpre, g_lnpre_w, g_lnpre_b,
                                    out=ws.get("dh", (B, S, D), bf16, dev))
         ops.gemm(GEMM_TN, EPI_F32_ADD, D, K, P, dx_raw[:, 1:], D, patches, K, g_conv, K, batch=B, a_bs=S * D, b_bs=P * K,
-                 splits=ops._wgrad_splits(B * P, D, K, dev))
+                 splits=0)
         ops.pos_table_bwd(dx_raw, g_cls, g_pos, g_tmp, T, G)
         ctx.saved = ctx.layers = ctx.misc = None
         flat_grads = [G_[k] for G_ in grads for k in E.BLOCK_KEYS]

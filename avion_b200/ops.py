@@ -142,19 +142,12 @@ def linear_dgrad(dy, w, epi=EPI_NONE, pre=None, out=None):
     return dx
 
 
-def _wgrad_splits(tokens, M, N, device):
-    sms = torch.cuda.get_device_properties(device).multi_processor_count
-    tiles = ((M + 127) // 128) * ((N + 255) // 256 if N % 256 == 0 else (N + 127) // 128)
-    kblocks = (tokens + 63) // 64
-    return max(1, min(kblocks, (2 * sms + tiles - 1) // tiles))
-
-
 def linear_wgrad(dy, x, dw):
     """dw[N,K] (fp32) += dy[tok,N]^T @ x[tok,K]."""
     _chk(dy, bf16, "dy"); _chk(x, bf16, "x"); _chk(dw, f32, "dw")
     N, K = dw.shape
     tok = dy.numel() // N
-    gemm(GEMM_TN, EPI_F32_ADD, N, K, tok, dy, N, x, K, dw, K, splits=_wgrad_splits(tok, N, K, dy.device))
+    gemm(GEMM_TN, EPI_F32_ADD, N, K, tok, dy, N, x, K, dw, K, splits=0)      # 0: the library picks the split-K count
     return dw
 
 

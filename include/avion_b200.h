@@ -73,7 +73,7 @@ typedef struct {
     void* C2;                                      /* same geometry as C */
     const float* bias;                             /* fp32 [N] */
     const void* R; int64_t ldr, r_batch_stride;    /* bf16, indexed like C */
-    int splits;                                    /* TN only: split of the contraction across CTAs (>=1) */
+    int splits;                                    /* TN only: split of the contraction across CTAs; 0 = chosen by the library */
 } avn_gemm_desc;
 int avn_gemm_bf16(const avn_gemm_desc* d, avn_stream_t stream);
 

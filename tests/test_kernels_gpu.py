@@ -70,7 +70,9 @@ def test_layernorm_fwd_bwd(ops, rows, D):
     assert rel_err(dc, dx.float().sum(0)) < 1e-4
 
 
-GEMM_SHAPES = [(256, 256, 128), (1000, 768, 768), (130, 384, 128), (2304, 3072, 768), (128 * 150, 768, 3072), (300, 200, 72)]
+# the last two are large enough for the CTA-pair (cta_group::2) kernels, with an odd number of ragged 128-row tiles
+GEMM_SHAPES = [(256, 256, 128), (1000, 768, 768), (130, 384, 128), (2304, 3072, 768), (128 * 150, 768, 3072), (300, 200, 72),
+               (128 * 201 + 37, 768, 256), (128 * 201 + 37, 256, 768)]
 
 
 @pytest.mark.parametrize("M,N,K", GEMM_SHAPES)

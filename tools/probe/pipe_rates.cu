@@ -15,6 +15,8 @@ __global__ void k(float* out, long long* cyc, float seed) {
 #pragma unroll 1
     for (int it = 0; it < 256; ++it) {
 #pragma unroll
+      for (int rep = 0; rep < 8; ++rep)
+#pragma unroll
         for (int i = 0; i < 8; i += 2) {
             if (OP == 0) {          // MUFU.EX2
                 asm volatile("ex2.approx.ftz.f32 %0, %0;" : "+f"(a[i]));
@@ -50,6 +52,7 @@ __global__ void k(float* out, long long* cyc, float seed) {
                 acc ^= r;
                 asm volatile("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(y0), "f"(y1));
                 acc += r;
+                a[i] = x0; a[i + 1] = x1;
             }
         }
     }
@@ -68,7 +71,7 @@ void run(const char* name, int per_iter) {
         k<OP><<<1, nw * 32>>>(out, cyc, 1.0f);
         k<OP><<<1, nw * 32>>>(out, cyc, 1.0f);
         long long c; cudaMemcpy(&c, cyc, 8, cudaMemcpyDeviceToHost);
-        const double n_inst = 256.0 * per_iter * (nw / 4);      // warp instructions per sub-partition
+        const double n_inst = 256.0 * 8 * per_iter * (nw / 4);      // warp instructions per sub-partition
         printf("%-28s %2d warps/SM (%d per sub-partition): %8lld cycles, %.2f cycles per warp-instruction per sub-partition\n", name, nw,
                nw / 4, c, c / n_inst);
     }
