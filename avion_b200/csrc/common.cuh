@@ -309,6 +309,13 @@ __device__ __forceinline__ float ex2(float x) {      // one MUFU.EX2, no range f
     return y;
 }
 
+// three-input maximum: one FMNMX3 (same issue cost as the two-input form on sm_100)
+__device__ __forceinline__ float fmax3(float a, float b, float c) {
+    float d;
+    asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+    return d;
+}
+
 // ---- small math -----------------------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
     __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
@@ -365,6 +372,15 @@ __device__ __forceinline__ float2 gelu_erf2(float2 x) {
     const float2 nax = make_float2(-fabsf(x.x), -fabsf(x.y));
     const float2 q = gelu_tail2(x, nax, e);
     return __ffma2_rn(nax, q, make_float2(fmaxf(x.x, 0.f), fmaxf(x.y, 0.f)));
+}
+// gelu(x) and gelu'(x) from one shared tail (one rcp + one ex2 per element for both)
+__device__ __forceinline__ void gelu_erf_both2(float2 x, float2& g, float2& dg) {
+    float2 e;
+    const float2 nax = make_float2(-fabsf(x.x), -fabsf(x.y));
+    const float2 q = gelu_tail2(x, nax, e);
+    g = __ffma2_rn(nax, q, make_float2(fmaxf(x.x, 0.f), fmaxf(x.y, 0.f)));
+    const float2 cdf = make_float2(x.x >= 0.f ? 1.0f - q.x : q.x, x.y >= 0.f ? 1.0f - q.y : q.y);
+    dg = __ffma2_rn(__fmul2_rn(x, make_float2(0.3989422804014327f, 0.3989422804014327f)), e, cdf);
 }
 __device__ __forceinline__ float2 gelu_erf_grad2(float2 x) {
     float2 e;

@@ -189,6 +189,22 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                 if (gtid < BN / 2) bias_s[gtid] = (p.bias != nullptr && n0 + gtid < p.N) ? p.bias[n0 + gtid] : 0.f;
                 named_bar_sync(bar_id, 128);
             }
+            // residual / pre-activation rows are fetched one 32-column unit ahead (the first one while the accumulator is
+            // still being computed): a row-per-thread global read has a long latency and nothing to hide behind otherwise
+            constexpr bool HAS_R = (EPI == AVN_EPI_BIAS_RESIDUAL || EPI == AVN_EPI_DGELU);
+            uint4 rnext[HAS_R ? 4 : 1];
+            auto fetch_r = [&](int u) {
+                if (HAS_R) {
+                    const int nc = n0 + u * 32;
+                    const __nv_bfloat16* rp = p.R + (long long)mb * p.r_batch_stride + (long long)m * p.ldr + nc;
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        rnext[i] = make_uint4(0, 0, 0, 0);
+                        if (m < p.M && nc + 8 * i + 8 <= p.N) rnext[i] = __ldg((const uint4*)(rp + 8 * i));
+                    }
+                }
+            };
+            fetch_r(0);
             mbar_wait(&tfull_bar[acc], acc_phase);
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN + g * (BN / 2);
@@ -228,27 +244,34 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                             f[j] = r0.x; f[j + 1] = r0.y; f[j + 2] = r1.x; f[j + 3] = r1.y;
                         }
                     }
-                    if (EPI == AVN_EPI_BIAS_RESIDUAL || EPI == AVN_EPI_DGELU) {
-                        const __nv_bfloat16* rp = p.R + (long long)mb * p.r_batch_stride + (long long)m * p.ldr + nc;
+                    if (HAS_R) {
+                        uint4 rcur[4];
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) rcur[i] = rnext[i];
+                        if (u + 1 < UNITS) fetch_r(u + 1);
 #pragma unroll
                         for (int i = 0; i < 4; ++i) {
-                            uint4 rv = make_uint4(0, 0, 0, 0);
-                            if (m < p.M && nc + 8 * i + 8 <= p.N) rv = __ldg((const uint4*)(rp + 8 * i));
+                            const uint4 rv = rcur[i];
                             const uint32_t rr[4] = {rv.x, rv.y, rv.z, rv.w};
 #pragma unroll
                             for (int e = 0; e < 4; ++e) {
                                 const float2 x = unpack_bf16(rr[e]);
                                 const float2 cur = make_float2(f[8 * i + 2 * e], f[8 * i + 2 * e + 1]);
-                                const float2 r = (EPI == AVN_EPI_BIAS_RESIDUAL) ? __fadd2_rn(cur, x) : __fmul2_rn(cur, gelu_erf_grad2(x));
+                                const float2 r = (EPI == AVN_EPI_BIAS_RESIDUAL) ? __fadd2_rn(cur, x) : __fmul2_rn(cur, x);     // DGELU: R holds gelu'(pre)
                                 f[8 * i + 2 * e] = r.x; f[8 * i + 2 * e + 1] = r.y;
                             }
                         }
                     }
-                    if (EPI == AVN_EPI_BIAS_GELU_DUAL) {
+                    if (EPI == AVN_EPI_BIAS_GELU_DUAL) {        // C = gelu(pre), C2 = gelu'(pre): what the backward of the MLP needs
 #pragma unroll
-                        for (int j = 0; j < 16; ++j) keep[(u & 1) * 16 + j] = pack_bf16(f[2 * j], f[2 * j + 1]);
+                        for (int j = 0; j < 16; ++j) {
+                            float2 g, dg;
+                            gelu_erf_both2(make_float2(f[2 * j], f[2 * j + 1]), g, dg);
+                            keep[(u & 1) * 16 + j] = pack_bf16(dg.x, dg.y);
+                            f[2 * j] = g.x; f[2 * j + 1] = g.y;
+                        }
                     }
-                    if (EPI == AVN_EPI_BIAS_GELU || EPI == AVN_EPI_BIAS_GELU_DUAL) {
+                    if (EPI == AVN_EPI_BIAS_GELU) {
 #pragma unroll
                         for (int j = 0; j < 32; j += 2) {
                             const float2 g = gelu_erf2(make_float2(f[j], f[j + 1]));
@@ -422,7 +445,7 @@ extern "C" int avn_gemm_bf16(const avn_gemm_desc* d, avn_stream_t stream_) {
         }
     } else if (d->mode == AVN_GEMM_NN) {
         AVN_REQUIRE(d->ldc % 8 == 0, "gemm: ldc must be a multiple of 8");
-        if (e == AVN_EPI_DGELU) AVN_REQUIRE(d->R != nullptr, "gemm: dgelu epilogue needs R (pre-activation)");
+        if (e == AVN_EPI_DGELU) AVN_REQUIRE(d->R != nullptr, "gemm: dgelu epilogue needs R (gelu' of the pre-activation)");
         switch (e) {
             case AVN_EPI_NONE: return launch_bn<AVN_GEMM_NN, AVN_EPI_NONE>(d, stream);
             case AVN_EPI_DGELU: return launch_bn<AVN_GEMM_NN, AVN_EPI_DGELU>(d, stream);

@@ -133,7 +133,8 @@ def linear_fwd(x, w, bias=None, epi=EPI_NONE, residual=None, out=None, out2=None
 
 
 def linear_dgrad(dy, w, epi=EPI_NONE, pre=None, out=None):
-    """dx[M,K] = epi(dy[M,N] @ w[N,K]); with EPI_DGELU: dx *= gelu'(pre[M,K])."""
+    """dx[M,K] = epi(dy[M,N] @ w[N,K]); with EPI_DGELU: dx *= pre[M,K], where pre = gelu'(pre-activation) is the second
+    output of linear_fwd(..., EPI_BIAS_GELU_DUAL)."""
     _chk(dy, bf16, "dy"); _chk(w, bf16, "w")
     N, K = w.shape
     M = dy.numel() // N
