@@ -5,9 +5,10 @@
 // One CTA per (clip, head, PAIR of 128-row query tiles).  Roles:
 //   warps 0-3 / 4-7 : softmax group 0 / 1 (one query row per thread: S row read once from TMEM, online softmax in fp32
 //                     registers with lazy rescaling, P written to swizzled smem as bf16, O accumulated in TMEM)
-//   warp 8          : MMA issuer  (S_w = Q_w K_j^T and O_w = P_w V_j on tcgen05, accumulators in TMEM)
+//   warps 8 / 10    : MMA issuer of group 0 / 1 (S_w = Q_w K_j^T and O_w = P_w V_j on tcgen05, accumulators in TMEM)
 //   warp 9          : TMA producer (Q tiles once, then a 3-stage K/V ring shared by both groups)
-// The two groups ping-pong: while one does softmax (MUFU/FMA bound at head dim 64) the other's MMAs run.
+// The two groups run half a tile period apart: while one exponentiates (MUFU bound at head dim 64) the other one loads its
+// S tile, finds the row maxima, stores P and waits; each group has its own MMA issuer so that nothing re-aligns them.
 #include "common.cuh"
 #include "../../include/avion_b200.h"
 
@@ -25,6 +26,20 @@ constexpr int OFF_BAR = OFF_V + KV_STAGES * KV_BYTES;
 constexpr int SMEM_TOTAL = OFF_BAR + 256 + 1024;
 // TMEM columns: S_w (fp32) at w*128, O_w (fp32) at 256 + w*64, P_w (bf16 pairs, the A operand of P V) at 384 + w*64
 constexpr uint32_t TM_S = 0, TM_O = 256, TM_P = 384;
+constexpr long long G1_LAG_CYCLES = 1200;      // head start of softmax group 0 over group 1
+
+// Optional phase trace (debug aid, off unless avn_debug_set_attn_fwd_trace is given a buffer): CTA (0,0,0) records clock64 at
+// phase boundaries as trace[(role * 32 + iteration) * 16 + slot]; role 0 / 1 = first warp of softmax group 0 / 1.
+// Compiled in only with -DAVN_TRACE (the extra predicated stores cost ~4 % in the softmax loop).
+__device__ long long* g_trace_fwd = nullptr;
+#ifdef AVN_TRACE
+#define TRF(role, it, slot)                                                                            \
+    do {                                                                                               \
+        if (trace && lane == 0 && (it) < 32) trace[((role) * 32 + (it)) * 16 + (slot)] = clock64();   \
+    } while (0)
+#else
+#define TRF(role, it, slot) do { } while (0)
+#endif
 
 struct Bars {
     uint64_t q_full;
@@ -88,12 +103,15 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
 #pragma unroll
     for (int w = 0; w < 2; ++w) nkv[w] = qt[w] >= q_tiles ? 0 : (causal ? min(kv_tiles, qt[w] + 1) : kv_tiles);
     const int nkv_max = max(nkv[0], nkv[1]);
+#ifdef AVN_TRACE
+    long long* trace = (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && (warp & 3) == 0 && warp < 8) ? g_trace_fwd : nullptr;
+#endif
 
     if (threadIdx.x == 0) {
         tma_prefetch_desc(&tmQKV);
         tma_prefetch_desc(&tmO);
         mbar_init(&bars->q_full, 1);
-        for (int i = 0; i < KV_STAGES; ++i) { mbar_init(&bars->kv_full[i], 1); mbar_init(&bars->kv_empty[i], 1); }
+        for (int i = 0; i < KV_STAGES; ++i) { mbar_init(&bars->kv_full[i], 1); mbar_init(&bars->kv_empty[i], 2); }
         for (int w = 0; w < 2; ++w) {
             mbar_init(&bars->s_full[w], 1); mbar_init(&bars->s_free[w], 128);
             mbar_init(&bars->p_ready[w], 128); mbar_init(&bars->o_full[w], 1);
@@ -107,8 +125,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
     const uint32_t tmem_base = bars->tmem_ptr;
 
     // the 8 math warps take the registers of the control warpgroup (setmaxnreg is per warpgroup: warps 8-11 all shrink)
-    if (warp >= 10) {
-        reg_dec<40>();       // idle warps: only complete the third warpgroup
+    if (warp == 11) {
+        reg_dec<40>();       // idle warp: only completes the third warpgroup
     } else if (warp == 9) {
         // ===================== TMA producer =====================
         // (the whole warp runs the loop and one elected lane issues, so addresses and coordinates stay in uniform registers)
@@ -129,14 +147,18 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
             }
             __syncwarp();
         }
-    } else if (warp == 8) {
-        // ===================== MMA issuer =====================
+    } else if (warp == 8 || warp == 10) {
+        // ===================== MMA issuers: one warp per softmax group =====================
+        // Two independent issuers keep the groups decoupled: with a single in-order issuer a group that runs behind stalls
+        // the other one's next S tile, which pulls both into lockstep - and then their MUFU-free phases (S load, row
+        // maxima, P store, waits) coincide and the MUFU pipe idles a third of the time.
         reg_dec<40>();
+        const int w = (warp == 8) ? 0 : 1;
         if (nkv_max > 0) {
             constexpr uint32_t idesc_s = umma_idesc_bf16(TILE, TILE, false, false);
             constexpr uint32_t idesc_o = umma_idesc_bf16(TILE, HD, false, true);
             // waits are executed by the whole warp, the MMAs by one elected lane (descriptors stay in uniform registers)
-            auto issue_s = [&](int w, int j) {
+            auto issue_s = [&](int j) {
                 if (j > 0) { mbar_wait(&bars->s_free[w], (j - 1) & 1); tc_fence_after(); }
                 if (elect_one()) {
                     const uint32_t qa = smem_u32(smem + OFF_Q + w * Q_BYTES);
@@ -152,16 +174,15 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
             mbar_wait(&bars->q_full, 0);
             mbar_wait(&bars->kv_full[0], 0);
             tc_fence_after();
-            for (int w = 0; w < 2; ++w) if (nkv[w] > 0) issue_s(w, 0);
+            if (nkv[w] > 0) issue_s(0);
             for (int j = 0; j < nkv_max; ++j) {
                 const int st = j % KV_STAGES;
                 if (j + 1 < nkv_max) {
                     mbar_wait(&bars->kv_full[(j + 1) % KV_STAGES], ((j + 1) / KV_STAGES) & 1);
                     tc_fence_after();
-                    for (int w = 0; w < 2; ++w) if (j + 1 < nkv[w]) issue_s(w, j + 1);
+                    if (j + 1 < nkv[w]) issue_s(j + 1);
                 }
-                for (int w = 0; w < 2; ++w) {
-                    if (j >= nkv[w]) continue;
+                if (j < nkv[w]) {
                     mbar_wait(&bars->p_ready[w], j & 1);
                     tc_fence_after();
                     if (elect_one()) {
@@ -174,6 +195,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
                     }
                     __syncwarp();
                 }
+                // both issuers release every K/V stage (one that has no work for tile j arrives as soon as the tile is loaded)
                 if (elect_one()) umma_commit(&bars->kv_empty[st]);
                 __syncwarp();
             }
@@ -194,20 +216,26 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
             // O accumulates in TMEM across K/V tiles (the MMA adds P_j V_j).  The softmax reference m_ref is only raised
             // when the running row maximum grows by more than 2^8 (lazy rescaling): then O (in TMEM) and l are rescaled.
             float m_ref = -INFINITY, l = 0.f;
+            // group 1 starts half a tile period late, so that its exponentials fall into group 0's MUFU-free phases
+            if (w == 1) { const long long t_start = clock64(); while (clock64() - t_start < G1_LAG_CYCLES) { } }
             for (int j = 0; j < n_my; ++j) {
                 const int kv0 = j * TILE;
                 const bool need_mask = (kv0 + TILE > S) || (causal && kv0 + TILE - 1 > q0);
                 const int limit = causal ? min(S - kv0, qrow - kv0 + 1) : (S - kv0);   // columns [0, limit) are valid
+                TRF(w, j, 0);
                 mbar_wait(&bars->s_full[w], j & 1);
                 tc_fence_after();
+                TRF(w, j, 1);
                 uint32_t sv[TILE];                 // this thread's row of S: one TMEM read, then S is handed back at once
 #pragma unroll
                 for (int c = 0; c < 4; ++c) tmem_ld32(t_s + c * 32, sv + c * 32);
                 tmem_ld_wait();
                 tc_fence_before();
                 mbar_arrive(&bars->s_free[w]);      // the MMA warp may now overwrite S with Q K_{j+1}^T
+                TRF(w, j, 2);
                 const float mx = need_mask ? row_max<true>(sv, limit) : row_max<false>(sv, limit);
                 const float mxs = mx * scale_log2;
+                TRF(w, j, 3);
                 const bool raise = mxs > m_ref + 8.0f;
                 const float m_new = raise ? mxs : m_ref;
                 const float alpha = raise ? ex2(m_ref - m_new) : 1.0f;
@@ -218,6 +246,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
                 if (need_mask) rs = row_exp<true>(sv, pk, scale_log2, m_ref, limit);
                 else rs = row_exp<false>(sv, pk, scale_log2, m_ref, limit);
                 l = fmaf(l, alpha, rs);
+                TRF(w, j, 4);
                 // P V of tile j-1 must have completed: the MMA has finished reading this group's P buffer and O is stable
                 if (j > 0) {
                     mbar_wait(&bars->o_full[w], (j - 1) & 1);
@@ -239,12 +268,14 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
                         tmem_st_wait();
                     }
                 }
+                TRF(w, j, 5);
                 // P -> TMEM as packed bf16 pairs (row = lane, 64 columns): the MMA reads it as its A operand
                 tmem_st32(t_p, pk);
                 tmem_st32(t_p + 32, pk + 32);
                 tmem_st_wait();
                 tc_fence_before();
                 mbar_arrive(&bars->p_ready[w]);
+                TRF(w, j, 6);
             }
             // all P V accumulated
             mbar_wait(&bars->o_full[w], (n_my - 1) & 1);
@@ -287,6 +318,11 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
     if (warp == 8) tmem_dealloc(tmem_base, 512);
 }
 }  // namespace
+
+extern "C" int avn_debug_set_attn_fwd_trace(long long* buf) {
+    AVN_CHECK_CUDA(cudaMemcpyToSymbol(g_trace_fwd, &buf, sizeof(buf)));
+    return AVN_OK;
+}
 
 extern "C" int avn_attn_fwd(const void* qkv, void* out, float* lse, int B, int S, int H, float scale, int causal, avn_stream_t stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;

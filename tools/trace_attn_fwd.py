@@ -1,4 +1,5 @@
-"""Phase timeline of attn_fwd for CTA (0,0,0): python tools/trace_attn_fwd.py [B].  Prints clock64 offsets per K/V tile."""
+"""Phase timeline of attn_fwd for CTA (0,0,0): python tools/trace_attn_fwd.py [B].  Prints clock64 offsets per K/V tile.
+Needs a library built with tracing: NVCC_APPEND_FLAGS=-DAVN_TRACE python avion_b200/csrc/build.py --force"""
 import ctypes
 import os
 import sys
