@@ -30,7 +30,7 @@ __global__ void transpose_cast_kernel(const float* __restrict__ src, __nv_bfloat
     }
 }
 
-// thread (cx, ry): 8 columns, rows ry + 8*(blockIdx.y + k*gridDim.y)
+// thread (cx, ry): 8 columns, rows ry + 8*(blockIdx.y + k*gridDim.y); four row loads in flight per thread
 __global__ void __launch_bounds__(256)
 colsum_kernel(const __nv_bfloat16* __restrict__ x, long long ld, float* __restrict__ out, long long rows, int cols) {
     __shared__ float red[8][32][8];
@@ -38,8 +38,22 @@ colsum_kernel(const __nv_bfloat16* __restrict__ x, long long ld, float* __restri
     const int c = (blockIdx.x * 32 + cx) * 8;
     float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     if (c < cols) {
-        for (long long r = (long long)blockIdx.y * 8 + ry; r < rows; r += (long long)gridDim.y * 8) {
-            const uint4 u = __ldg((const uint4*)(x + r * ld + c));
+        const long long step = (long long)gridDim.y * 8;
+        const __nv_bfloat16* xp = x + c;
+        long long r = (long long)blockIdx.y * 8 + ry;
+        for (; r + 3 * step < rows; r += 4 * step) {
+            uint4 u[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) u[k] = __ldg((const uint4*)(xp + (r + k * step) * ld));
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const uint32_t w[4] = {u[k].x, u[k].y, u[k].z, u[k].w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) { const float2 f = unpack_bf16(w[e]); acc[2 * e] += f.x; acc[2 * e + 1] += f.y; }
+            }
+        }
+        for (; r < rows; r += step) {
+            const uint4 u = __ldg((const uint4*)(xp + r * ld));
             const uint32_t w[4] = {u.x, u.y, u.z, u.w};
 #pragma unroll
             for (int e = 0; e < 4; ++e) { const float2 f = unpack_bf16(w[e]); acc[2 * e] += f.x; acc[2 * e + 1] += f.y; }
@@ -175,7 +189,7 @@ extern "C" int avn_colsum_bf16(const void* x, int64_t ld, float* colsum, int64_t
     AVN_REQUIRE(x && colsum && rows > 0 && cols > 0, "colsum: bad arguments");
     AVN_REQUIRE(cols % 8 == 0 && ld % 8 == 0 && ((uintptr_t)x % 16) == 0, "colsum: cols/ld must be multiples of 8 and x 16-byte aligned");
     const int gx = (cols + 255) / 256;
-    long long gy = (2LL * avn_num_sms() + gx - 1) / gx;
+    long long gy = (8LL * avn_num_sms() + gx - 1) / gx;      // eight resident CTAs per SM
     const long long maxy = (rows + 7) / 8;
     if (gy > maxy) gy = maxy;
     colsum_kernel<<<dim3(gx, (unsigned)gy), 256, 0, (cudaStream_t)stream_>>>((const __nv_bfloat16*)x, ld, colsum, rows, cols);
