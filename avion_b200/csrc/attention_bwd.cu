@@ -37,6 +37,20 @@ struct Bars {
 };
 static_assert(sizeof(Bars) <= 256, "barrier block");
 
+// Of every AVN_BWD_POLY_DEN element pairs, AVN_BWD_POLY_NUM take the FMA-pipe exponential (common.cuh: exp2_poly2).  Off by
+// default: unlike the forward kernel this one is not MUFU-bound (1/4 .. 1/2 polynomial measured 2-4 % slower) - it saturates
+// the shared-memory data pipe (ncu: tensor operand fetch 45 % + LSU wavefronts 50 %).
+#ifndef AVN_BWD_POLY_NUM
+#define AVN_BWD_POLY_NUM 0
+#endif
+#ifndef AVN_BWD_POLY_DEN
+#define AVN_BWD_POLY_DEN 3
+#endif
+__device__ __forceinline__ float2 exp2_pair_bwd(float2 x, int pair_index) {
+    if ((pair_index % AVN_BWD_POLY_DEN) < AVN_BWD_POLY_NUM) return exp2_poly2(x);
+    return make_float2(ex2(x.x), ex2(x.y));
+}
+
 // One 32-column chunk of a key row: P^T = exp2(S^T*scale_log2 + nl[q]), dS^T = P^T o (dP^T*scale + nd[q]) -> packed bf16.
 // nl = -LSE*log2e (or -inf for query rows past the end), nd = -delta*scale; both broadcast from smem.
 template <bool MASK>
@@ -48,7 +62,7 @@ __device__ __forceinline__ void pds_chunk(const uint32_t* sv, const uint32_t* dv
         const float4 l4 = *(const float4*)(nl + i), d4 = *(const float4*)(nd + i);
         const float2 x0 = __ffma2_rn(make_float2(__uint_as_float(sv[i]), __uint_as_float(sv[i + 1])), sc2, make_float2(l4.x, l4.y));
         const float2 x1 = __ffma2_rn(make_float2(__uint_as_float(sv[i + 2]), __uint_as_float(sv[i + 3])), sc2, make_float2(l4.z, l4.w));
-        float2 p0 = make_float2(ex2(x0.x), ex2(x0.y)), p1 = make_float2(ex2(x1.x), ex2(x1.y));
+        float2 p0 = exp2_pair_bwd(x0, i >> 1), p1 = exp2_pair_bwd(x1, (i >> 1) + 1);
         if (MASK) {               // causal: query column c is visible to this key row only if c >= first_valid
             if (i < first_valid) p0.x = 0.f;
             if (i + 1 < first_valid) p0.y = 0.f;

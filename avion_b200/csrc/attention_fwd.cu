@@ -66,32 +66,6 @@ __device__ __forceinline__ float row_max(const uint32_t* sv, int limit) {
     return fmaxf(fmaxf(a, b), fmaxf(c, d));
 }
 
-// exp2 of a pair on the FMA pipe instead of the MUFU: x = j + f with j = rint(x) (magic-number add), 2^f by a minimax quartic
-// on [-0.5, 0.5] (relative error 2.7e-6; a cubic's 7.5e-5 is smooth in f, does not average out like rounding noise and moved
-// the tiny-batch golden loss by 1e-3), 2^j added into the exponent field.  x <= ~8 here; the clamp keeps the exponent arithmetic in range for hopeless scores.
-#ifndef AVN_FWD_POLY_DEGREE
-#define AVN_FWD_POLY_DEGREE 3
-#endif
-__device__ __forceinline__ float2 exp2_poly2(float2 x) {
-    x.x = fmaxf(x.x, -126.f); x.y = fmaxf(x.y, -126.f);
-    const float2 big = make_float2(12582912.f, 12582912.f), nbig = make_float2(-12582912.f, -12582912.f);
-    const float2 r = __fadd2_rn(x, big);                 // low mantissa bits of r = j
-    const float2 jf = __fadd2_rn(r, nbig);
-    const float2 f = __fadd2_rn(x, make_float2(-jf.x, -jf.y));
-#if AVN_FWD_POLY_DEGREE == 4
-    float2 p = __ffma2_rn(make_float2(0.00957010221f, 0.00957010221f), f, make_float2(0.0559178591f, 0.0559178591f));
-    p = __ffma2_rn(p, f, make_float2(0.240247443f, 0.240247443f));
-    p = __ffma2_rn(p, f, make_float2(0.693121791f, 0.693121791f));
-    p = __ffma2_rn(p, f, make_float2(0.999999285f, 0.999999285f));
-#else
-    float2 p = __ffma2_rn(make_float2(0.0551716685f, 0.0551716685f), f, make_float2(0.242611125f, 0.242611125f));
-    p = __ffma2_rn(p, f, make_float2(0.693260968f, 0.693260968f));
-    p = __ffma2_rn(p, f, make_float2(0.999928057f, 0.999928057f));
-#endif
-    return make_float2(__int_as_float(__float_as_int(p.x) + (__float_as_int(r.x) << 23)),
-                       __int_as_float(__float_as_int(p.y) + (__float_as_int(r.y) << 23)));
-}
-
 // Of every AVN_FWD_POLY_DEN score pairs, AVN_FWD_POLY_NUM take the FMA-pipe exponential: the MUFU pipe (16 results per clock
 // per SM) is what bounds this kernel at head dim 64, and its instructions queue behind TMEM and shared-memory traffic.
 #ifndef AVN_FWD_POLY_NUM
