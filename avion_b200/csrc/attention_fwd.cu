@@ -26,7 +26,7 @@ constexpr int OFF_BAR = OFF_V + KV_STAGES * KV_BYTES;
 constexpr int SMEM_TOTAL = OFF_BAR + 256 + 1024;
 // TMEM columns: S_w (fp32) at w*128, O_w (fp32) at 256 + w*64, P_w (bf16 pairs, the A operand of P V) at 384 + w*64
 constexpr uint32_t TM_S = 0, TM_O = 256, TM_P = 384;
-constexpr long long G1_LAG_CYCLES = 1200;      // head start of softmax group 0 over group 1
+constexpr long long G1_LAG_CYCLES = 1000;      // head start of softmax group 0 over group 1
 
 // Optional phase trace (debug aid, off unless avn_debug_set_attn_fwd_trace is given a buffer): CTA (0,0,0) records clock64 at
 // phase boundaries as trace[(role * 32 + iteration) * 16 + slot]; role 0 / 1 = first warp of softmax group 0 / 1.
@@ -229,14 +229,17 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
             // O accumulates in TMEM across K/V tiles (the MMA adds P_j V_j).  The softmax reference m_ref is only raised
             // when the running row maximum grows by more than 2^8 (lazy rescaling): then O (in TMEM) and l are rescaled.
             float m_ref = -INFINITY, l = 0.f;
-            // group 1 starts half a tile period late, so that its exponentials fall into group 0's MUFU-free phases
-            if (w == 1) { const long long t_start = clock64(); while (clock64() - t_start < G1_LAG_CYCLES) { } }
             for (int j = 0; j < n_my; ++j) {
                 const int kv0 = j * TILE;
                 const bool need_mask = (kv0 + TILE > S) || (causal && kv0 + TILE - 1 > q0);
                 const int limit = causal ? min(S - kv0, qrow - kv0 + 1) : (S - kv0);   // columns [0, limit) are valid
                 TRF(w, j, 0);
                 mbar_wait(&bars->s_full[w], j & 1);
+                // Group 1 starts its first tile half a period late, so that its exponentials fall into group 0's MUFU-free
+                // phases (S load, row maxima, P store, barrier round trips) and vice versa.  The offset persists: each group's
+                // period is its own dependency chain.  (The delay has to sit here, after the first S tile exists - before
+                // the loop it disappears in the ~3500-cycle prologue both groups wait through.)
+                if (w == 1 && j == 0) { const long long t_start = clock64(); while (clock64() - t_start < G1_LAG_CYCLES) { } }
                 tc_fence_after();
                 TRF(w, j, 1);
                 uint32_t sv[TILE];                 // this thread's row of S: one TMEM read, then S is handed back at once
