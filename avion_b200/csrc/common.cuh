@@ -225,9 +225,16 @@ __device__ __forceinline__ void umma_commit_2cta(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
                  ::"r"(smem_u32(bar)), "h"((uint16_t)3) : "memory");
 }
-// arrive on the leader CTA's copy of a barrier (from either CTA of the pair)
+// arrive on the leader CTA's copy of a barrier (from either CTA of the pair).  Relaxed: the only thing the waiter needs
+// ordered - this thread's tcgen05.ld of the accumulator - has completed (tcgen05.wait::ld) before the arrive is issued; a
+// .release.cluster arrive costs a cluster-scope memory barrier (ERRBAR + MEMBAR: 10 % of the stall samples of the epilogue
+// warps of the GELU GEMMs, which always have stores in flight).
 __device__ __forceinline__ void mbar_arrive_leader(uint64_t* bar) {
+#ifdef AVN_ARRIVE_RELEASE
     asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(leader_smem_addr(bar)) : "memory");
+#else
+    asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(leader_smem_addr(bar)) : "memory");
+#endif
 }
 
 // Instruction descriptor: bf16 x bf16 -> fp32, M x N tile (cute::UMMA::InstrDescriptor bit layout).
