@@ -3,8 +3,8 @@
 // (scripts/main_lavila_pretrain.py:816-817) and the einops patchify (avion/models/transformer.py:319).
 //
 // One CTA per (clip, frame, patch-row): it stages the p image rows of the crop (p x 3*crop bytes) in shared memory
-// with 16-byte global loads, then writes the gw consecutive output tokens (one contiguous gw*3*p*p bf16 block) with
-// 16-byte stores.  Normalisation goes through a 3x256 bf16 table built with the same fp32 (x-mean)/std division as
+// with 16-byte global loads, then writes the gw consecutive output tokens (one contiguous block of gw token rows, each
+// 3*p*p features rounded up to a multiple of 8 with zero padding) with 16-byte stores.  Normalisation goes through a 3x256 bf16 table built with the same fp32 (x-mean)/std division as
 // the reference, so every output equals bf16(reference fp32 value) bit for bit.
 #include "common.cuh"
 #include "../../include/avion_b200.h"
@@ -57,24 +57,49 @@ clip_transform_kernel(const uint8_t* __restrict__ frames, __nv_bfloat16* __restr
         *(uint4*)(rows + sh * pitch + ch * 16) = v;
     }
     __syncthreads();
-    // write gw tokens x (3*p*p) features, 8 features (16 B) per thread-iteration
+    // write gw tokens x (3*p*p) features, 8 features (16 B) per thread-iteration.  A token row is 3*p*p features rounded
+    // up to a multiple of 8 (zero padding: ViT-L/14 has 588 -> 592), so every row starts on a 16-byte boundary.
     const int feat = 3 * p * p;
-    const int vec_per_tok = feat / 8;
-    const int p8 = p / 8;                                    // 8-pixel groups per patch row
-    __nv_bfloat16* out = patches + ((long long)(b * T + t) * gh * gw + (long long)hh * gw) * feat;
-    for (int o = threadIdx.x; o < gw * vec_per_tok; o += blockDim.x) {
-        const int ww = o / vec_per_tok, f8 = o % vec_per_tok;
-        const int c = f8 / (p * p8), sh = (f8 / p8) % p, sw0 = (f8 % p8) * 8;
-        const uint8_t* r = rows + sh * pitch + mis[sh];
-        const __nv_bfloat16* l = lut + c * 256;
-        __nv_bfloat16 v[8];
+    const int feat_pad = (feat + 7) & ~7;
+    const int vec_per_tok = feat_pad / 8;
+    __nv_bfloat16* out = patches + ((long long)(b * T + t) * gh * gw + (long long)hh * gw) * feat_pad;
+    if ((p & 7) == 0) {
+        const int p8 = p / 8;                                    // 8-pixel groups per patch row
+        for (int o = threadIdx.x; o < gw * vec_per_tok; o += blockDim.x) {
+            const int ww = o / vec_per_tok, f8 = o % vec_per_tok;
+            const int c = f8 / (p * p8), sh = (f8 / p8) % p, sw0 = (f8 % p8) * 8;
+            const uint8_t* r = rows + sh * pitch + mis[sh];
+            const __nv_bfloat16* l = lut + c * 256;
+            __nv_bfloat16 v[8];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            int px = ww * p + sw0 + i;
-            if (flip) px = crop - 1 - px;
-            v[i] = l[r[px * 3 + c]];
+            for (int i = 0; i < 8; ++i) {
+                int px = ww * p + sw0 + i;
+                if (flip) px = crop - 1 - px;
+                v[i] = l[r[px * 3 + c]];
+            }
+            *(uint4*)(out + (long long)o * 8) = *(uint4*)v;
         }
-        *(uint4*)(out + (long long)o * 8) = *(uint4*)v;
+    } else {
+        // patch sizes that are not a multiple of 8 (14): a 16-byte output vector straddles patch rows, so each of its 8
+        // features is located on its own (feature f = c*p*p + sh*p + sw)
+        const int pp = p * p;
+        for (int o = threadIdx.x; o < gw * vec_per_tok; o += blockDim.x) {
+            const int ww = o / vec_per_tok, f0 = (o % vec_per_tok) * 8;
+            __nv_bfloat16 v[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int f = f0 + i;
+                if (f < feat) {
+                    const int c = f / pp, sh = (f % pp) / p, sw = f % p;
+                    int px = ww * p + sw;
+                    if (flip) px = crop - 1 - px;
+                    v[i] = lut[c * 256 + rows[sh * pitch + mis[sh] + px * 3 + c]];
+                } else {
+                    v[i] = __float2bfloat16_rn(0.f);
+                }
+            }
+            *(uint4*)(out + (long long)o * 8) = *(uint4*)v;
+        }
     }
 }
 }  // namespace
@@ -84,7 +109,7 @@ extern "C" int avn_clip_transform_u8_bf16(const uint8_t* frames, void* patches, 
     cudaStream_t stream = (cudaStream_t)stream_;
     AVN_REQUIRE(frames && patches && mean3 && std3, "clip_transform: null pointer");
     AVN_REQUIRE(B > 0 && T > 0 && crop > 0 && patch > 0, "clip_transform: bad sizes");
-    AVN_REQUIRE(crop % patch == 0 && patch % 8 == 0 && patch <= 64, "clip_transform: patch must divide crop and be a multiple of 8 (<= 64)");
+    AVN_REQUIRE(crop % patch == 0 && patch <= 64, "clip_transform: patch must divide crop (<= 64)");
     AVN_REQUIRE(crop <= Hs && crop <= Ws && crop <= 512, "clip_transform: crop %d exceeds source %dx%d or 512", crop, Hs, Ws);
     AVN_REQUIRE(((uintptr_t)patches % 16) == 0, "clip_transform: output must be 16-byte aligned");
     const int pitch = ((crop * 3 + 15) / 16) * 16 + 32;

@@ -66,6 +66,13 @@ def CLIP_VITB16(freeze_temperature=False, use_grad_checkpointing=False, use_bidi
                   project_embed_dim, freeze_temperature, use_grad_checkpointing, pretrain_zoo, pretrain_path)
 
 
-def CLIP_VITL14(*args, **kwargs):
-    """avion/models/model_clip.py:180-259.  Patch 14 needs a K=588 -> 640 padded patchify."""
-    raise NotImplementedError("ViT-L/14 is a later row of the scope table (patch 14 is not a multiple of 8)")
+def CLIP_VITL14(freeze_temperature=False, use_grad_checkpointing=False, use_bidirectional_lm=False, context_length=77,
+                vocab_size=49408, patch_dropout=0.0, drop_path_rate=0.0, num_frames=1, use_fast_conv1=True, use_flash_attn=True,
+                project_embed_dim=512, pretrain_zoo="random", pretrain_path=None, **kwargs):
+    """avion/models/model_clip.py:180-259 (ViT-L/14 video tower: 24 blocks, width 1024, 16 heads; 12L/768 text tower).
+    Patch 14: token rows are 588 features padded to 592 (16-byte rows); conv1.weight keeps the reference shape [1024, 588]."""
+    return _build(dict(image_size=224, patch_size=14, width=1024, layers=24, heads=16, mlp_ratio=4, patch_dropout=patch_dropout,
+                       drop_path_rate=drop_path_rate, num_frames=num_frames),
+                  dict(context_length=context_length, vocab_size=vocab_size, width=768, heads=12, layers=12,
+                       causal_mask=not use_bidirectional_lm),
+                  project_embed_dim, freeze_temperature, use_grad_checkpointing, pretrain_zoo, pretrain_path)

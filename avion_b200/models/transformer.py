@@ -128,6 +128,10 @@ class _VisionTowerFn(torch.autograd.Function):
         save = any(ctx.needs_input_grad)      # False under torch.no_grad() or with frozen parameters
         layers = E.cast_layers(_unflatten(flat))
         conv_bf = ops.cast_bf16(conv_w.detach())
+        if conv_w.shape[1] != K:              # patch rows are padded to a multiple of 8 features (ViT-L/14: 588 -> 592)
+            padded = torch.zeros(D, K, dtype=bf16, device=dev)
+            padded[:, :conv_w.shape[1]] = conv_bf
+            conv_bf = padded
         table = ops.pos_table_fwd(cls.detach(), pos.detach(), temporal.detach() if temporal is not None else None, T, G)
         x_raw = torch.empty(B, S, D, dtype=bf16, device=dev)
         # conv1 (fast_conv1 Linear, no bias) + positional/temporal table, written straight into rows 1.. of [B,S,D]
@@ -162,7 +166,7 @@ class _VisionTowerFn(torch.autograd.Function):
         grads = E.zero_grads(_unflatten(flat))
         g_cls, g_pos, g_proj = E._zeros_like_f32(cls), E._zeros_like_f32(pos), E._zeros_like_f32(proj)
         g_tmp = E._zeros_like_f32(temporal) if temporal is not None else None
-        g_conv = E._zeros_like_f32(conv_w)
+        g_conv = torch.zeros(conv_w.shape[0], K, dtype=f32, device=dev)
         g_lnpre_w, g_lnpre_b = E._zeros_like_f32(lnpre_w), E._zeros_like_f32(lnpre_b)
         g_lnpost_w, g_lnpost_b = E._zeros_like_f32(lnpost_w), E._zeros_like_f32(lnpost_b)
         # head: only the CLS rows of dL/dx are non-zero
@@ -179,6 +183,8 @@ class _VisionTowerFn(torch.autograd.Function):
         ops.pos_table_bwd(dx_raw, g_cls, g_pos, g_tmp, T, G)
         ctx.saved = ctx.layers = ctx.misc = None
         flat_grads = [G_[k] for G_ in grads for k in E.BLOCK_KEYS]
+        if conv_w.shape[1] != K:
+            g_conv = g_conv[:, :conv_w.shape[1]].contiguous()
         return (None, None, g_cls, g_pos, g_tmp, g_proj, g_conv, g_lnpre_w, g_lnpre_b, g_lnpost_w, g_lnpost_b, *flat_grads)
 
 
@@ -197,7 +203,6 @@ class VisionTransformer(nn.Module):
         assert patch_dropout == 0. and drop_rate == 0. and attn_drop_rate == 0. and drop_path_rate == 0., \
             "dropout variants are not implemented on the B200 path"
         assert ln_pre and output_dim is not None and act_layer is nn.GELU
-        assert patch_size % 8 == 0, "patch size must be a multiple of 8 (ViT-L/14 is a later row, SURVEY.md 8f)"
         self.use_fast_conv1, self.use_flash_attn = True, True     # parameter naming of the flash + fast_conv1 reference
         self.image_size, self.patch_size = (image_size, image_size), (patch_size, patch_size)
         self.width, self.output_dim = width, output_dim
@@ -246,12 +251,15 @@ class VisionTransformer(nn.Module):
             assert x.dim() == 5 and x.shape[1] == self.num_frames
             return ops.clip_transform(x.contiguous(), self.image_size[0], p, self.mean, self.std)
         if x.dim() == 3:
+            assert x.shape[2] == ops.patch_features(p), "pre-computed patches must use the padded row length of GPUClipTransform"
             return x.to(bf16).contiguous()
         if x.dim() == 4:
             x = x.unsqueeze(2)
         B, C, T, H, W = x.shape        # layout glue for the float entry only (index permutation of transformer.py:319)
         gh, gw = H // p, W // p
         x = x.reshape(B, C, T, gh, p, gw, p).permute(0, 2, 3, 5, 1, 4, 6).reshape(B, T * gh * gw, C * p * p)
+        if ops.patch_features(p) != C * p * p:
+            x = torch.nn.functional.pad(x, (0, ops.patch_features(p) - C * p * p))
         return x.to(bf16).contiguous()
 
     def _run(self, x, normalize):

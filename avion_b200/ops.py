@@ -65,14 +65,19 @@ def sample_rrc_boxes(seed, n, src_w, src_h, scale=(0.5, 1.0), ratio=(3.0 / 4.0, 
     return out
 
 
+def patch_features(patch):
+    """Row length of a patch token: 3*patch^2 rounded up to 8 elements (16-byte rows for TMA; ViT-L/14: 588 -> 592)."""
+    return (3 * patch * patch + 7) // 8 * 8
+
+
 def clip_transform(frames_u8, crop, patch, mean, std, boxes=None, out=None):
-    """uint8 [B,T,Hs,Ws,3] -> bf16 patches [B, T*(crop/patch)^2, 3*patch^2]."""
+    """uint8 [B,T,Hs,Ws,3] -> bf16 patches [B, T*(crop/patch)^2, F], F = 3*patch^2 rounded up to a multiple of 8 (zero pad)."""
     _chk(frames_u8, torch.uint8, "frames")
     B, T, Hs, Ws, ch = frames_u8.shape
     assert ch == 3
     g = crop // patch
     if out is None:
-        out = torch.empty(B, T * g * g, 3 * patch * patch, dtype=bf16, device=frames_u8.device)
+        out = torch.empty(B, T * g * g, patch_features(patch), dtype=bf16, device=frames_u8.device)
     if boxes is not None:
         _chk(boxes, torch.int32, "boxes")
         assert boxes.shape == (B, 3) and boxes.device == frames_u8.device

@@ -32,7 +32,8 @@ int avn_sample_rrc_boxes(uint64_t seed, int n, int src_w, int src_h, double scal
  * Replaces frames.astype(float32) (avion/data/clip_dataset.py:104,164), permute + kornia Normalize
  * (scripts/main_lavila_pretrain.py:816-817) and the einops patchify (avion/models/transformer.py:319) in one pass.
  * frames: u8 [B][T][Hs][Ws][3]; boxes: device int32 [B][3] = (x, y, hflip) or NULL (x=y=0, no flip);
- * patches: bf16 [B][T*gh*gw][3*patch*patch], token = t*gh*gw + hh*gw + ww, feature = c*p*p + sh*p + sw. */
+ * patches: bf16 [B][T*gh*gw][F], F = 3*patch*patch rounded up to a multiple of 8 (zero padding; 588 -> 592 for ViT-L/14),
+ * token = t*gh*gw + hh*gw + ww, feature = c*p*p + sh*p + sw. */
 int avn_clip_transform_u8_bf16(const uint8_t* frames, void* patches, int B, int T, int Hs, int Ws, int crop, int patch,
                                const int32_t* boxes, const float* mean3 /* host */, const float* std3 /* host */,
                                avn_stream_t stream);

@@ -59,6 +59,8 @@ class ClipCfg:
 
 TINY = ClipCfg(image_size=64, patch=16, width=128, layers=2, heads=2, frames=4, embed_dim=64,
                ctx=77, vocab=512, t_width=128, t_heads=2, t_layers=2)
+TINY14 = ClipCfg(image_size=56, patch=14, width=128, layers=2, heads=2, frames=4, embed_dim=64,
+                 ctx=77, vocab=512, t_width=128, t_heads=2, t_layers=2)      # patch 14 (588 features per token) like ViT-L/14
 VITB16_4F = ClipCfg(frames=4)          # BASELINE.json configs[0]
 VITB16_16F = ClipCfg(frames=16)        # BASELINE.json configs[1]
 VITL14_16F = ClipCfg(patch=14, width=1024, layers=24, heads=16, frames=16, t_width=768, t_heads=12)

@@ -66,4 +66,5 @@ if __name__ == "__main__":
     torch.manual_seed(0)
     run("tiny_b6", O.TINY, 6, 0, 1234, backward=True)
     run("tiny_b32", O.TINY, 32, 1, 99, backward=True)
+    run("tiny14_b32", O.TINY14, 32, 2, 77, backward=True)          # patch 14: the ViT-L/14 patchify / padded conv1 path
     run("vitb16_4f_b8", O.VITB16_4F, 8, 0, 1234, backward=False)   # BASELINE.json configs[0]

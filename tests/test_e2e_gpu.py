@@ -33,7 +33,7 @@ def run_step(cfg, sd, clips, tokens, backward=True):
     return model, img.detach().cpu(), txt.detach().cpu(), out
 
 
-@pytest.mark.parametrize("name", ["tiny_b6", "tiny_b32"])
+@pytest.mark.parametrize("name", ["tiny_b6", "tiny_b32", "tiny14_b32"])      # tiny14: patch 14, the ViT-L/14 patchify path
 def test_tiny_step_matches_reference_golden(name):
     g, cfg = load_golden(name)
     sd = O.make_state_dict(cfg, int(g["wseed"]))

@@ -41,6 +41,22 @@ def test_clip_transform_bit_exact(ops, shape):
     assert torch.equal(got.cpu(), ref)
 
 
+@pytest.mark.parametrize("shape", [(2, 3, 56, 56, 14), (1, 2, 224, 224, 14)])
+def test_clip_transform_patch14_bit_exact(ops, shape):
+    """ViT-L/14 patchify: 588 features per token, rows zero-padded to 592 (16-byte rows for TMA)."""
+    B, T, H, W, p = shape
+    clips = torch.from_numpy(np.random.RandomState(3).randint(0, 256, (B, T, H, W, 3)).astype(np.uint8))
+    ref = O.patchify(O.clip_transform(clips), p).to(bf16)
+    got = ops.clip_transform(clips.cuda(), H, p, O.MEAN_OPENAI, O.STD_OPENAI).cpu()
+    assert got.shape[-1] == 592
+    assert torch.equal(got[..., :588], ref)
+    assert torch.count_nonzero(got[..., 588:]) == 0
+    boxes = torch.tensor([[0, 0, 1]] * B, dtype=torch.int32)
+    ref_f = O.patchify(O.clip_transform(O.crop_clip(clips, boxes, (H, W))), p).to(bf16)
+    got_f = ops.clip_transform(clips.cuda(), H, p, O.MEAN_OPENAI, O.STD_OPENAI, boxes=boxes.cuda()).cpu()
+    assert torch.equal(got_f[..., :588], ref_f)
+
+
 def test_clip_transform_crop_flip_bit_exact(ops):
     B, T, Hs, Ws, crop, p = 4, 3, 101, 157, 64, 16
     clips = torch.from_numpy(np.random.RandomState(2).randint(0, 256, (B, T, Hs, Ws, 3)).astype(np.uint8))

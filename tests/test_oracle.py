@@ -18,7 +18,7 @@ def load_golden(name):
     return g, cfg
 
 
-@pytest.mark.parametrize("name", ["tiny_b6", "tiny_b32"])
+@pytest.mark.parametrize("name", ["tiny_b6", "tiny_b32", "tiny14_b32"])
 def test_oracle_matches_golden_fwd_bwd(name):
     g, cfg = load_golden(name)
     sd = O.make_state_dict(cfg, int(g["wseed"]))
