@@ -22,7 +22,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 # algorithmic FLOPs per clip-text pair, forward; train step = 3x (no recompute counted)
-FWD_GFLOP_PER_PAIR = {"vitb16_16f": 905.3, "vitb16_4f": 162.95}
+FWD_GFLOP_PER_PAIR = {"vitb16_16f": 905.3, "vitb16_4f": 162.95, "vitl14_16f": 4142.8}
 
 
 def peaks():
@@ -163,7 +163,7 @@ def run_ours(args):
     from torch.nn.parallel import DistributedDataParallel as DDP
     from avion_b200 import _lib, ops
     from avion_b200.losses import ClipLoss
-    from avion_b200.models import CLIP_VITB16
+    from avion_b200.models import CLIP_VITB16, CLIP_VITL14
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -179,7 +179,8 @@ def run_ours(args):
     cfg = SimpleNamespace(frames=args.frames, image_size=224, vocab=49408, ctx=77)
     B = args.batch
     torch.manual_seed(0)
-    model = CLIP_VITB16(num_frames=args.frames, project_embed_dim=256, pretrain_zoo="random").to(dev)
+    factory = CLIP_VITL14 if args.model == "vitl14" else CLIP_VITB16      # vitl14 = BASELINE.json configs[3]
+    model = factory(num_frames=args.frames, project_embed_dim=256, pretrain_zoo="random").to(dev)
     with torch.no_grad():
         model.visual.temporal_embedding.normal_(std=0.02)
     net = DDP(model, device_ids=[local_rank], bucket_cap_mb=200, gradient_as_bucket_view=True) if world > 1 else model
@@ -297,7 +298,7 @@ def run_ours(args):
     if top:
         roofline = {"kernel": top["kernel"], "bound": top["bound"], "achieved": top["achieved"], "peak": top["peak"], "unit": top["unit"],
                     "frac": top["frac"], "traffic": traffic, "peak_source": pk["source"] + " (sustained: timed inside the step)"}
-    key = "vitb16_16f" if args.frames == 16 else ("vitb16_4f" if args.frames == 4 else None)
+    key = {("vitb16", 16): "vitb16_16f", ("vitb16", 4): "vitb16_4f", ("vitl14", 16): "vitl14_16f"}.get((args.model, args.frames))
     step_tf = None
     if key:
         step_tf = 3 * FWD_GFLOP_PER_PAIR[key] * 1e9 * B / (ms_step * 1e-3) / 1e12
@@ -313,10 +314,12 @@ def run_ours(args):
                         "sample": f"oracle port (fp32 PyTorch restatement of the reference path), {pairs} clip-text pairs, one "
                                   f"fwd+ClipLoss+bwd+AdamW step, no warm-up ({ms / 1e3:.1f} s)"}
 
-    line = {"metric": "clips/sec ViT-B/16 16f CLIP train step", "value": value, "unit": "clips/s", "n_gpus": world,
+    arch = "ViT-L/14" if args.model == "vitl14" else "ViT-B/16"
+    which = "configs[3]" if args.model == "vitl14" else "configs[1]"
+    line = {"metric": f"clips/sec {arch} 16f CLIP train step", "value": value, "unit": "clips/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": f"AVION CLIP ViT-B/16 {args.frames}f 224^2 full train step, {B} clips/GPU (BASELINE.json configs[1])",
+            "config": {"workload": f"AVION CLIP {arch} {args.frames}f 224^2 full train step, {B} clips/GPU (BASELINE.json {which})",
                        "clips_per_gpu": B, "global_batch": world * B, "frames": args.frames, "embed_dim": 256, "optimizer": "AdamW(fused)",
                        "parallelism": f"dp{world}", "l2": "inputs_exceed_l2 (617 MB uint8 clips + GB-scale activations per step)"},
             "loss": loss_val, "gpu_launches": launches,
@@ -338,6 +341,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=256, help="clips per GPU")
     ap.add_argument("--frames", type=int, default=16)
+    ap.add_argument("--model", default="vitb16", choices=["vitb16", "vitl14"], help="vitl14: BASELINE.json configs[3], use --batch 64")
     ap.add_argument("--cpu-pairs", type=int, default=2)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
