@@ -95,26 +95,33 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restr
                 if (drr) ur[j] = __ldg(drr + i);
             }
         }
-        float s1 = 0.f, s2 = 0.f;
+        // all the per-element arithmetic is packed f32x2 (FFMA2 / FADD2 / FMUL2): this kernel is as much issue-bound as
+        // memory-bound (~800 scalar instructions per row per warp before)
+        const float2 rs2 = make_float2(rstd, rstd), nmr2 = make_float2(-mean * rstd, -mean * rstd);
+        float2 s1v = make_float2(0.f, 0.f), s2v = make_float2(0.f, 0.f);
 #pragma unroll
         for (int j = 0; j < VPL; ++j) {
             const int i = lane + 32 * j;
             if (i < nvec) {
                 const uint32_t wx[4] = {ux[j].x, ux[j].y, ux[j].z, ux[j].w}, wd[4] = {ud[j].x, ud[j].y, ud[j].z, ud[j].w};
                 const float4 g0 = __ldg((const float4*)(gamma + i * 8)), g1 = __ldg((const float4*)(gamma + i * 8 + 4));
-                const float g[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+                const float2 g[4] = {make_float2(g0.x, g0.y), make_float2(g0.z, g0.w), make_float2(g1.x, g1.y), make_float2(g1.z, g1.w)};
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
-                    const float2 fx = unpack_bf16(wx[e]), fd = unpack_bf16(wd[e]);
-                    const float h0 = (fx.x - mean) * rstd, h1 = (fx.y - mean) * rstd;
-                    ag[j][2 * e] = fmaf(fd.x, h0, ag[j][2 * e]); ag[j][2 * e + 1] = fmaf(fd.y, h1, ag[j][2 * e + 1]);
-                    ab[j][2 * e] += fd.x; ab[j][2 * e + 1] += fd.y;
-                    const float t0 = fd.x * g[2 * e], t1 = fd.y * g[2 * e + 1];
-                    s1 += t0 + t1; s2 = fmaf(t0, h0, fmaf(t1, h1, s2));
+                    const float2 fd = unpack_bf16(wd[e]);
+                    const float2 h = __ffma2_rn(unpack_bf16(wx[e]), rs2, nmr2);       // (x - mean) * rstd
+                    float2 a = make_float2(ag[j][2 * e], ag[j][2 * e + 1]), bsum = make_float2(ab[j][2 * e], ab[j][2 * e + 1]);
+                    a = __ffma2_rn(fd, h, a);
+                    bsum = __fadd2_rn(bsum, fd);
+                    ag[j][2 * e] = a.x; ag[j][2 * e + 1] = a.y; ab[j][2 * e] = bsum.x; ab[j][2 * e + 1] = bsum.y;
+                    const float2 t = __fmul2_rn(fd, g[e]);
+                    s1v = __fadd2_rn(s1v, t);
+                    s2v = __ffma2_rn(t, h, s2v);
                 }
             }
         }
-        const float c1 = warp_sum(s1) / D, c2 = warp_sum(s2) / D;
+        const float c1 = warp_sum(s1v.x + s1v.y) / D, c2 = warp_sum(s2v.x + s2v.y) / D;
+        const float2 nc1 = make_float2(-c1, -c1), nc2 = make_float2(-c2, -c2);
         uint4* dxr = (uint4*)(dx + row * D);
 #pragma unroll
         for (int j = 0; j < VPL; ++j) {
@@ -123,18 +130,18 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restr
                 const uint32_t wx[4] = {ux[j].x, ux[j].y, ux[j].z, ux[j].w}, wd[4] = {ud[j].x, ud[j].y, ud[j].z, ud[j].w};
                 const uint32_t wr[4] = {ur[j].x, ur[j].y, ur[j].z, ur[j].w};
                 const float4 g0 = __ldg((const float4*)(gamma + i * 8)), g1 = __ldg((const float4*)(gamma + i * 8 + 4));
-                const float g[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+                const float2 g[4] = {make_float2(g0.x, g0.y), make_float2(g0.z, g0.w), make_float2(g1.x, g1.y), make_float2(g1.z, g1.w)};
                 uint32_t po[4];
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
-                    const float2 fx = unpack_bf16(wx[e]), fd = unpack_bf16(wd[e]), fr = unpack_bf16(wr[e]);
-                    const float h0 = (fx.x - mean) * rstd, h1 = (fx.y - mean) * rstd;
-                    const float o0 = fmaf(rstd, fd.x * g[2 * e] - c1 - h0 * c2, fr.x);
-                    const float o1 = fmaf(rstd, fd.y * g[2 * e + 1] - c1 - h1 * c2, fr.y);
-                    po[e] = pack_bf16(o0, o1);
+                    const float2 h = __ffma2_rn(unpack_bf16(wx[e]), rs2, nmr2);
+                    float2 u = __ffma2_rn(unpack_bf16(wd[e]), g[e], nc1);            // dy*g - c1
+                    u = __ffma2_rn(h, nc2, u);                                          //       - h*c2
+                    const float2 o = __ffma2_rn(u, rs2, unpack_bf16(wr[e]));           // * rstd + residual gradient
+                    po[e] = pack_bf16(o.x, o.y);
                     if (dcolsum) {   // column sum of the values actually stored (bf16-rounded), as the next consumer sees them
-                        const float2 f = unpack_bf16(po[e]);
-                        ac[j][2 * e] += f.x; ac[j][2 * e + 1] += f.y;
+                        const float2 c = __fadd2_rn(make_float2(ac[j][2 * e], ac[j][2 * e + 1]), unpack_bf16(po[e]));
+                        ac[j][2 * e] = c.x; ac[j][2 * e + 1] = c.y;
                     }
                 }
                 dxr[i] = make_uint4(po[0], po[1], po[2], po[3]);
