@@ -3,12 +3,15 @@
 This is the host-side "runtime" of the hot path: no autograd tracing inside a tower - each tower is ONE
 torch.autograd.Function whose forward launches the kernels in order and keeps exactly the activations the
 hand-written backward needs (per block: block input, qkv, attention output + LSE, post-attention residual, LayerNorm
-statistics).  LayerNorm outputs and the MLP hidden activations are recomputed in the backward (selective recompute:
+statistics).  The MLP hidden activations - and, unless HBM clearly has room for them (keep_ln_outputs), the LayerNorm
+outputs - are recomputed in the backward (selective recompute:
 +~4.6 % FLOPs instead of the reference's whole-block checkpoint, +33 %), which is what lets 256 clips x 3137 tokens
 x 12 blocks fit in 180 GB.
 
 Reference semantics: avion/models/transformer.py:144-150 (block), :309-378 (video tower), :455-478 (text tower).
 """
+import os
+
 import torch
 
 from .. import ops
@@ -24,6 +27,7 @@ class Workspace:
 
     def __init__(self):
         self.buf = {}
+        self.flags = {}
 
     def get(self, name, shape, dtype, device):
         t = self.buf.get(name)
@@ -40,24 +44,45 @@ def _zeros_like_f32(p):
     return torch.zeros(p.shape, dtype=f32, device=p.device)
 
 
+def keep_ln_outputs(B, S, D, n_layers, dev, margin=24e9):
+    """Keep the two LayerNorm outputs of every block for the backward (2 x 2 bytes x B*S*D per block: 29.6 GB for 256 clips of
+    ViT-B/16 16f) instead of recomputing them, when HBM clearly has the room: free memory now, minus what this forward will
+    save anyway (x, qkv, o, x_mid per block), the workspaces and the extra LayerNorm outputs, must leave `margin` bytes."""
+    force = os.environ.get("AVN_KEEP_LN")       # "0" / "1" override the memory test
+    if force is not None:
+        return force == "1"
+    bsd = float(B) * S * D
+    need = (12.0 * n_layers + 32.0 + 4.0 * n_layers) * bsd
+    free, _ = torch.cuda.mem_get_info(dev)
+    return free + torch.cuda.memory_reserved(dev) - torch.cuda.memory_allocated(dev) - need >= margin
+
+
 def blocks_forward(x, layers, heads, eps, causal, ws, save):
     """x bf16 [B,S,D] -> x_out; `layers` = list of dicts (BLOCK_KEYS; matrices already bf16).  Returns (x, saved list)."""
     B, S, D = x.shape
     dev = x.device
     scale = 64 ** -0.5
     saved = []
+    key = ("keep_ln", B, S, D, len(layers))
+    if save and key not in ws.flags:          # decided once per shape, at the first training forward
+        ws.flags[key] = keep_ln_outputs(B, S, D, len(layers), dev)
+    keep = save and ws.flags[key]
     for L in layers:
-        h = ws.get("h", (B, S, D), bf16, dev)
+        h = torch.empty(B, S, D, dtype=bf16, device=dev) if keep else ws.get("h", (B, S, D), bf16, dev)
+        h1 = h if keep else None
         _, m1, r1 = ops.layernorm_fwd(x, L["ln1_w"], L["ln1_b"], eps, out=h, save_stats=save)
         qkv = ops.linear_fwd(h, L["qkv_w"], L["qkv_b"], EPI_BIAS) if save else \
             ops.linear_fwd(h, L["qkv_w"], L["qkv_b"], EPI_BIAS, out=ws.get("qkv", (B, S, 3 * D), bf16, dev))
         o, lse = ops.attn_fwd(qkv, heads, scale, causal, out=None if save else ws.get("o", (B, S, D), bf16, dev))
         x_mid = ops.linear_fwd(o, L["out_w"], L["out_b"], EPI_BIAS_RESIDUAL, residual=x)
+        if keep:
+            h = torch.empty(B, S, D, dtype=bf16, device=dev)
+        h2 = h if keep else None
         _, m2, r2 = ops.layernorm_fwd(x_mid, L["ln2_w"], L["ln2_b"], eps, out=h, save_stats=save)
         a = ops.linear_fwd(h, L["fc1_w"], L["fc1_b"], EPI_BIAS_GELU, out=ws.get("a", (B, S, L["fc1_w"].shape[0]), bf16, dev))
         x_out = ops.linear_fwd(a, L["fc2_w"], L["fc2_b"], EPI_BIAS_RESIDUAL, residual=x_mid)
         if save:
-            saved.append((x, m1, r1, qkv, o, lse, x_mid, m2, r2))
+            saved.append((x, m1, r1, qkv, o, lse, x_mid, m2, r2, h1, h2))
         x = x_out
     return x, saved
 
@@ -72,11 +97,14 @@ def blocks_backward(g, saved, layers, grads, heads, eps, causal, ws, last_colsum
     fc2_bias_done = last_colsum_done
     for li in range(n_layers - 1, -1, -1):
         L, G = layers[li], grads[li]
-        x_in, m1, r1, qkv, o, lse, x_mid, m2, r2 = saved.pop()
+        x_in, m1, r1, qkv, o, lse, x_mid, m2, r2, h1, h2 = saved.pop()
         Hd = L["fc1_w"].shape[0]
         # ---- MLP half: x_out = x_mid + fc2(gelu(fc1(ln_2(x_mid))))
-        h = ws.get("h", (B, S, D), bf16, dev)
-        ops.layernorm_fwd(x_mid, L["ln2_w"], L["ln2_b"], eps, out=h, save_stats=False)
+        if h2 is not None:
+            h = h2                                  # kept by the forward (keep_ln_outputs)
+        else:
+            h = ws.get("h", (B, S, D), bf16, dev)
+            ops.layernorm_fwd(x_mid, L["ln2_w"], L["ln2_b"], eps, out=h, save_stats=False)
         a = ws.get("a", (B, S, Hd), bf16, dev)
         pre = ws.get("pre", (B, S, Hd), bf16, dev)      # receives gelu'(fc1 pre-activation)
         ops.linear_fwd(h, L["fc1_w"], L["fc1_b"], EPI_BIAS_GELU_DUAL, out=a, out2=pre)
@@ -96,7 +124,12 @@ def blocks_backward(g, saved, layers, grads, heads, eps, causal, ws, last_colsum
                             dq_acc=ws.get("dq_acc", (B, S, D), f32, dev))
         del qkv, o, lse
         ops.colsum(dqkv, G["qkv_b"])
-        ops.layernorm_fwd(x_in, L["ln1_w"], L["ln1_b"], eps, out=h, save_stats=False)
+        del h, h2
+        if h1 is not None:
+            h = h1
+        else:
+            h = ws.get("h", (B, S, D), bf16, dev)
+            ops.layernorm_fwd(x_in, L["ln1_w"], L["ln1_b"], eps, out=h, save_stats=False)
         ops.linear_wgrad(dqkv, h, G["qkv_w"])
         dh1 = ops.linear_dgrad(dqkv, L["qkv_w"], out=dh)
         # dL/dx_in = g1 + LN1'(dh1); its column sum is the fc2 bias gradient of the block below
@@ -105,7 +138,7 @@ def blocks_backward(g, saved, layers, grads, heads, eps, causal, ws, last_colsum
         ops.layernorm_bwd(dh1, x_in, L["ln1_w"], m1, r1, G["ln1_w"], G["ln1_b"], dres=g1, dcolsum=below, out=g_new)
         g = g_new
         fc2_bias_done = True
-        del x_in, x_mid
+        del x_in, x_mid, h, h1
     return g
 
 
