@@ -26,7 +26,10 @@ constexpr int OFF_BAR = OFF_V + KV_STAGES * KV_BYTES;
 constexpr int SMEM_TOTAL = OFF_BAR + 256 + 1024;
 // TMEM columns: S_w (fp32) at w*128, O_w (fp32) at 256 + w*64, P_w (bf16 pairs, the A operand of P V) at 384 + w*64
 constexpr uint32_t TM_S = 0, TM_O = 256, TM_P = 384;
-constexpr long long G1_LAG_CYCLES = 1000;      // head start of softmax group 0 over group 1
+#ifndef AVN_FWD_LAG
+#define AVN_FWD_LAG 1000
+#endif
+constexpr long long G1_LAG_CYCLES = AVN_FWD_LAG;      // head start of softmax group 0 over group 1
 
 // Optional phase trace (debug aid, off unless avn_debug_set_attn_fwd_trace is given a buffer): CTA (0,0,0) records clock64 at
 // phase boundaries as trace[(role * 32 + iteration) * 16 + slot]; role 0 / 1 = first warp of softmax group 0 / 1.
