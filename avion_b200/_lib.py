@@ -47,11 +47,15 @@ SIGNATURES = {
     "avn_head_bwd": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp],
     "avn_infonce_fwd": [_vp, _vp, _vp, _vp, _f, _i, _i, _i, _i, _vp, _vp, _vp],
     "avn_infonce_bwd": [_vp, _vp, _vp, _vp, _f, _i, _i, _i, _i, _vp, _f, _vp, _vp, _vp, _vp],
+    "avn_adamw_chunk_elems": [],
+    "avn_adamw_step": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _f, _f, _f, _f, _i, _vp],
+    "avn_clamp_scalar_f32": [_vp, _f, _f, _vp],
 }
 
 # kernels launched per C-ABI call (for the bench's gpu_launches count); default 1
 KERNELS_PER_CALL = {"avn_attn_bwd": 3, "avn_infonce_bwd": 3, "avn_head_bwd": 2, "avn_pos_table_bwd": 2,
-                    "avn_token_embed_bwd": 2, "avn_sample_rrc_boxes": 0, "avn_device_check": 0, "avn_version": 0}
+                    "avn_token_embed_bwd": 2, "avn_sample_rrc_boxes": 0, "avn_device_check": 0, "avn_version": 0,
+                    "avn_adamw_chunk_elems": 0}
 launch_count = 0
 
 _lib = None

@@ -136,6 +136,17 @@ int avn_infonce_bwd(const float* img, const float* txt, const float* all_img, co
                     int n, int N, int E, int row_offset, const float* lse, float gscale, float* dlogits, float* d_all,
                     float* dscale, avn_stream_t stream);
 
+/* ---- O1: optimizer step (scripts/main_lavila_pretrain.py:296-341 AdamW with weight-decay / no-decay groups; :880 clamp) --
+ * One launch updates every tensor: device tables of n tensors (params, grads, exp_avg, exp_avg_sq: fp32 pointers; sizes in
+ * elements; weight_decay per tensor) and a device chunk table (tensor index, element offset; avn_adamw_chunk_elems()
+ * elements per chunk).  Decoupled AdamW in the operation order of torch.optim.AdamW; `step` counts from 1. */
+int avn_adamw_chunk_elems(void);
+int avn_adamw_step(void* const* params, const void* const* grads, void* const* exp_avg, void* const* exp_avg_sq,
+                   const int64_t* sizes, const float* weight_decay, const int32_t* chunk_tensor, const int64_t* chunk_offset,
+                   int n_chunks, float lr, float beta1, float beta2, float eps, int step, avn_stream_t stream);
+/* logit_scale.data.clamp_(0, 4.6052) (main_lavila_pretrain.py:880) without a host round trip */
+int avn_clamp_scalar_f32(float* x, float lo, float hi, avn_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

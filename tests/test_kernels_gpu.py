@@ -265,3 +265,34 @@ def test_infonce_fwd_bwd(ops, n, N, E, off):
                                     off, lse, 1.0)
     assert rel_err(d_all[0], ai.grad) < 1e-4 and rel_err(d_all[1], at.grad) < 1e-4
     assert abs(float(dscale) - float(sc.grad)) < 1e-4 * max(1.0, abs(float(sc.grad)))
+
+
+def test_fused_adamw_matches_torch(ops):
+    """O1: one-launch multi-tensor AdamW == torch.optim.AdamW (two groups as in main_lavila_pretrain.py:296-320)."""
+    from avion_b200.optim import FusedAdamW, clamp_logit_scale
+    torch.manual_seed(5)
+    shapes = [(1,), (7,), (1000, 33), (16384 * 2 + 5,), (768, 768), ()]
+    ref = [torch.nn.Parameter(torch.randn(s, device="cuda")) for s in shapes]
+    # an odd-offset view: exercises the unaligned (scalar) path
+    base = torch.randn(4099, device="cuda")
+    ref.append(torch.nn.Parameter(base[3:]))
+    ours = [torch.nn.Parameter(p.detach().clone()) if i < len(shapes) else torch.nn.Parameter(base.clone()[3:])
+            for i, p in enumerate(ref)]
+    groups = lambda ps: [{"params": ps[:3], "weight_decay": 0.01}, {"params": ps[3:], "weight_decay": 0.0}]   # noqa: E731
+    o_ref = torch.optim.AdamW(groups(ref), lr=3e-3, betas=(0.9, 0.98), eps=1e-8)
+    o_our = FusedAdamW(groups(ours), lr=3e-3, betas=(0.9, 0.98), eps=1e-8)
+    for step in range(5):
+        for a, b in zip(ref, ours):
+            g = torch.randn_like(a)
+            a.grad = g.clone()
+            b.grad = g.clone()
+        o_ref.step()
+        o_our.step()
+    for a, b in zip(ref, ours):
+        assert torch.allclose(a, b, rtol=2e-6, atol=1e-7), float((a - b).abs().max())
+    sd = o_our.state_dict()
+    assert set(sd["state"][0].keys()) == {"step", "exp_avg", "exp_avg_sq"} and float(sd["state"][0]["step"]) == 5
+    o_ref.load_state_dict(sd)                        # checkpoints are interchangeable
+    ls = torch.nn.Parameter(torch.tensor(5.0, device="cuda"))
+    clamp_logit_scale(ls)
+    assert abs(float(ls) - 4.6052) < 1e-6
