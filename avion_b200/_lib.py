@@ -50,12 +50,19 @@ SIGNATURES = {
     "avn_adamw_chunk_elems": [],
     "avn_adamw_step": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _f, _f, _f, _f, _i, _vp],
     "avn_clamp_scalar_f32": [_vp, _f, _f, _vp],
+    "avn_tube_mask_slots": [_vp, _vp, _vp, _vp, _i, _i, _vp],
+    "avn_tubelet_transform_u8": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, C.POINTER(_f), C.POINTER(_f), _vp],
+    "avn_gather_rows_f32_bf16": [_vp, _vp, _i64, _vp, _i, _vp, _i, _i, _i, _vp],
+    "avn_colsum_batched_bf16": [_vp, _i, _i64, _i, _i, _vp, _vp],
+    "avn_mse_workspace_floats": [],
+    "avn_mse_fwd": [_vp, _vp, _i64, _vp, _vp, _vp],
+    "avn_mse_bwd": [_vp, _vp, _vp, _i64, _vp, _vp],
 }
 
 # kernels launched per C-ABI call (for the bench's gpu_launches count); default 1
 KERNELS_PER_CALL = {"avn_attn_bwd": 3, "avn_infonce_bwd": 3, "avn_head_bwd": 2, "avn_pos_table_bwd": 2,
                     "avn_token_embed_bwd": 2, "avn_sample_rrc_boxes": 0, "avn_device_check": 0, "avn_version": 0,
-                    "avn_adamw_chunk_elems": 0}
+                    "avn_adamw_chunk_elems": 0, "avn_mse_workspace_floats": 0, "avn_mse_fwd": 2}
 launch_count = 0
 
 _lib = None

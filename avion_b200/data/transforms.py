@@ -27,3 +27,29 @@ class GPUClipTransform(nn.Module):
     @staticmethod
     def sample_boxes(seed, n, src_w, src_h, **kw):
         return ops.sample_rrc_boxes(seed, n, src_w, src_h, **kw)
+
+
+class TubeMaskingGeneratorGPU:
+    """avion/data/transforms.py:279-302: one random spatial mask per clip, repeated over the tubelet time steps.  Same torch
+    RNG calls as the reference (so the same seed gives the same masks); the result is returned on `device` as bool [B, N]
+    already flattened (the train loop's `.flatten(1).to(torch.bool)`, scripts/main_videomae_pretrain.py:319, is a no-op on it)."""
+
+    def __init__(self, batch, input_size, mask_ratio, device=0):
+        self.batch = batch
+        self.frames, self.height, self.width = input_size
+        self.num_patches_per_frame = self.height * self.width
+        self.total_patches = self.frames * self.num_patches_per_frame
+        self.num_masks_per_frame = int(mask_ratio * self.num_patches_per_frame)
+        self.total_masks = self.frames * self.num_masks_per_frame
+        self.device = device
+
+    def __repr__(self):
+        return "Maks: total patches {}, mask patches {}".format(self.total_patches, self.total_masks)
+
+    def __call__(self):
+        tensors = torch.zeros((self.batch, self.num_patches_per_frame))
+        indexes = torch.argsort(torch.rand(self.batch, self.num_patches_per_frame))[:, :self.num_masks_per_frame]
+        tensors[torch.arange(self.batch).unsqueeze(1), indexes] = 1
+        masks = tensors.repeat(1, self.frames)
+        dev = self.device if isinstance(self.device, (str, torch.device)) else torch.device("cuda", self.device)
+        return masks.to(dev, non_blocking=True).to(torch.bool)

@@ -1,1 +1,1 @@
-from .losses import ClipLoss  # noqa: F401
+from .losses import ClipLoss, MSELoss  # noqa: F401

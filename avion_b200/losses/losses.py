@@ -67,3 +67,24 @@ class ClipLoss(nn.Module):
         loss, acc = _InfoNCEFn.apply(image_features, text_features, logit_scale, self.rank, self.world_size, self.local_loss,
                                      self.gather_with_grad, self.group)
         return {"loss": loss, "clip_acc": acc}
+
+
+class _MSEFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, pred, target):
+        loss = ops.mse_fwd(pred, target)
+        ctx.save_for_backward(pred, target)
+        return loss
+
+    @staticmethod
+    def backward(ctx, gloss):
+        pred, target = ctx.saved_tensors
+        return ops.mse_bwd(pred, target, gloss.to(torch.float32).reshape(1).contiguous()), None
+
+
+class MSELoss(nn.Module):
+    """torch.nn.MSELoss() of the VideoMAE step (scripts/main_videomae_pretrain.py:129,341): mean((input - target)^2) with bf16
+    predictions and fp32 targets, deterministic two-stage reduction, fused (pred - target) backward."""
+
+    def forward(self, input, target):
+        return _MSEFn.apply(input.contiguous(), target.contiguous())

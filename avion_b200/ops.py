@@ -287,3 +287,73 @@ def infonce_bwd(img, txt, all_img, all_txt, scale, row_offset, lse, gscale):
     _lib.call("avn_infonce_bwd", _p(img), _p(txt), _p(all_img), _p(all_txt), float(scale), n, N, E, row_offset, _p(lse),
               float(gscale), _p(dlogits), _p(d_all), _p(dscale), _stream(img))
     return d_all, dscale
+
+
+# ---- VideoMAE pretraining step (csrc/videomae.cu) -----------------------------------------------------------------
+def tube_mask_slots(mask):
+    """mask bool/uint8 [B,N] (True = masked) -> (slot int32 [B,N], order int32 [B,N], counts int32 [B])."""
+    if mask.dtype == torch.bool:
+        mask = mask.view(torch.uint8)
+    _chk(mask, torch.uint8, "mask")
+    B, N = mask.shape
+    slot = torch.empty(B, N, dtype=torch.int32, device=mask.device)
+    order = torch.empty(B, N, dtype=torch.int32, device=mask.device)
+    counts = torch.empty(B, dtype=torch.int32, device=mask.device)
+    _lib.call("avn_tube_mask_slots", _p(mask), _p(slot), _p(order), _p(counts), B, N, _stream(mask))
+    return slot, order, counts
+
+
+def tubelet_transform(frames_u8, slot, n_visible, patch, mean, std, want_patches=True, want_targets=True):
+    """uint8 [B,T,crop,crop,3] -> (patches bf16 [B,n_visible,6*p*p] of the visible tokens, targets fp32 [B,N-n_visible,6*p*p]
+    of the masked tokens); see include/avion_b200.h."""
+    _chk(frames_u8, torch.uint8, "frames"); _chk(slot, torch.int32, "slot")
+    B, T, Hs, Ws, ch = frames_u8.shape
+    assert ch == 3 and Hs == Ws, "the VideoMAE entry takes square clips already cropped (fused decode-crop output)"
+    N = (T // 2) * (Hs // patch) ** 2
+    assert slot.shape == (B, N)
+    F = 6 * patch * patch
+    dev = frames_u8.device
+    patches = torch.empty(B, n_visible, F, dtype=bf16, device=dev) if want_patches else None
+    targets = torch.empty(B, N - n_visible, F, dtype=f32, device=dev) if want_targets else None
+    m = (C.c_float * 3)(*[float(v) for v in mean])
+    s = (C.c_float * 3)(*[float(v) for v in std])
+    work = float(frames_u8.numel()) * (1.0 + (2.0 * n_visible + 4.0 * (N - n_visible)) / N)
+    with _timed("tubelet_transform", frames_u8, work):
+        _lib.call("avn_tubelet_transform_u8", _p(frames_u8), _p(slot), _p(patches), _p(targets), B, T, Hs, patch, n_visible, m, s,
+                  _stream(frames_u8))
+    return patches, targets
+
+
+def gather_rows(table, order, n, add_row=None, add_from=0):
+    """out bf16 [B,n,D] = table[order[b,:n]] (+ add_row on rows >= add_from)."""
+    _chk(table, f32, "table"); _chk(order, torch.int32, "order")
+    B, N = order.shape
+    D = table.shape[1]
+    out = torch.empty(B, n, D, dtype=bf16, device=table.device)
+    _lib.call("avn_gather_rows_f32_bf16", _p(table), _p(order), N, _p(add_row), add_from, _p(out), B, n, D, _stream(table))
+    return out
+
+
+def colsum_batched(x, B, batch_stride, rows, cols, out):
+    """out[cols] (fp32) += sum over batches and rows of a [rows, cols] bf16 block at x + b*batch_stride."""
+    _chk(out, f32, "out")
+    _lib.call("avn_colsum_batched_bf16", _p(x), B, batch_stride, rows, cols, _p(out), _stream(x))
+    return out
+
+
+def mse_fwd(pred, target):
+    _chk(pred, bf16, "pred"); _chk(target, f32, "target")
+    assert pred.shape == target.shape
+    ws = torch.empty(_lib.load().avn_mse_workspace_floats(), dtype=f32, device=pred.device)
+    loss = torch.empty((), dtype=f32, device=pred.device)
+    with _timed("mse", pred, 6.0 * pred.numel()):
+        _lib.call("avn_mse_fwd", _p(pred), _p(target), pred.numel(), _p(ws), _p(loss), _stream(pred))
+    return loss
+
+
+def mse_bwd(pred, target, gloss):
+    _chk(gloss, f32, "gloss")
+    dpred = torch.empty_like(pred)
+    with _timed("mse", pred, 8.0 * pred.numel()):
+        _lib.call("avn_mse_bwd", _p(pred), _p(target), _p(gloss), pred.numel(), _p(dpred), _stream(pred))
+    return dpred

@@ -22,7 +22,8 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 # algorithmic FLOPs per clip-text pair, forward; train step = 3x (no recompute counted)
-FWD_GFLOP_PER_PAIR = {"vitb16_16f": 905.3, "vitb16_4f": 162.95, "vitl14_16f": 4142.8}
+FWD_GFLOP_PER_PAIR = {"vitb16_16f": 905.3, "vitb16_4f": 162.95, "vitl14_16f": 4142.8,
+                      "videomae_16f": 70.9}      # per clip: encoder 31.82 + enc->dec 0.09 + decoder (4 L) 37.30 + head 1.66
 
 
 def peaks():
@@ -136,6 +137,28 @@ def cpu_reference_clips_per_s(cfg, pairs, steps, warmup, threads):
     return pairs / mean, mean * 1e3
 
 
+def cpu_reference_videomae_clips_per_s(clips_n, steps, warmup, threads):
+    """VideoMAE pretraining step (oracle port, fp32) on the host cores: targets + forward + MSE + backward + AdamW."""
+    from oracle import videomae_oracle as V
+    torch.set_num_threads(threads)
+    cfg = V.VITB16
+    sd = {k: v.clone().requires_grad_(True) for k, v in V.make_state_dict(cfg, 0).items()}
+    opt = torch.optim.AdamW(list(sd.values()), lr=1.5e-4, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.05)
+    clips, mask = V.make_inputs(cfg, clips_n, 1234)
+    times = []
+    for it in range(warmup + steps):
+        t0 = time.perf_counter()
+        opt.zero_grad(set_to_none=True)
+        out = V.train_step_forward(sd, clips, mask, cfg)
+        out["loss"].backward()
+        opt.step()
+        dt = time.perf_counter() - t0
+        if it >= warmup:
+            times.append(dt)
+    mean = sum(times) / len(times)
+    return clips_n / mean, mean * 1e3
+
+
 def run_reference(args):
     from oracle import clip_oracle as O
     rank = int(os.environ.get("RANK", "0"))
@@ -144,6 +167,19 @@ def run_reference(args):
     cfg = O.VITB16_16F if args.frames == 16 else O.ClipCfg(frames=args.frames)
     threads = os.cpu_count() or 1
     pairs = args.cpu_pairs
+    if args.model == "videomae":
+        steps, warmup = min(args.steps, 2), min(args.warmup, 1)
+        n = max(pairs, 4)
+        v, ms = cpu_reference_videomae_clips_per_s(n, steps, warmup, threads)
+        sample = f"{n} clips/step, fp32, targets+fwd+MSE+bwd+AdamW, {steps} timed steps after {warmup} warm-up"
+        print(json.dumps({"impl": "reference", "metric": "clips/sec VideoMAE ViT-B/16 16f pretrain step", "value": v, "unit": "clips/s",
+                          "n_gpus": args.gpus, "steps": steps, "warmup": warmup, "ms_per_step": ms, "higher_is_better": True,
+                          "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                          "config": {"workload": "VideoMAE ViT-B/16 16f 224^2 pretrain step, 90% tube masking (oracle port on host CPU)",
+                                     "clips_per_step": n},
+                          "cpu_baseline": {"value": v, "unit": "clips/s", "cores": threads, "kind": "port", "sample": sample},
+                          "e2e": {"value": v, "unit": "clips/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}), flush=True)
+        return
     # bound the whole run to a few minutes: at most 2 timed + 1 warm-up CPU steps of `pairs` pairs (each ~10-40 s)
     steps, warmup = min(args.steps, 2), min(args.warmup, 1)
     v, ms = cpu_reference_clips_per_s(cfg, pairs, steps, warmup, threads)
@@ -179,6 +215,9 @@ def run_ours(args):
     cfg = SimpleNamespace(frames=args.frames, image_size=224, vocab=49408, ctx=77)
     B = args.batch
     torch.manual_seed(0)
+    mae = args.model == "videomae"               # BASELINE.json configs[4]
+    if mae:
+        return run_videomae(args, world, rank, local_rank, dev)
     factory = CLIP_VITL14 if args.model == "vitl14" else CLIP_VITB16      # vitl14 = BASELINE.json configs[3]
     model = factory(num_frames=args.frames, project_embed_dim=256, pretrain_zoo="random").to(dev)
     with torch.no_grad():
@@ -340,19 +379,166 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+# =====================================================================================================================
+def run_videomae(args, world, rank, local_rank, dev):
+    """BASELINE.json configs[4]: VideoMAE ViT-B/16 pretrain step (scripts/main_videomae_pretrain.py:316-352): tube mask ->
+    fused transform (visible patches + standardised targets) -> encoder on visible tokens -> decoder -> MSE -> backward ->
+    gradient all-reduce (DDP) -> AdamW."""
+    import torch.distributed as dist
+    from torch.nn.parallel import DistributedDataParallel as DDP
+    from avion_b200 import _lib, ops
+    from avion_b200.data.transforms import TubeMaskingGeneratorGPU
+    from avion_b200.losses import MSELoss
+    from avion_b200.models import VIDEOMAE_VITB16
+    from avion_b200.optim import FusedAdamW
+
+    B = args.batch
+    model = VIDEOMAE_VITB16(decoder_depth=4).to(dev)
+    net = DDP(model, device_ids=[local_rank], bucket_cap_mb=200, gradient_as_bucket_view=True) if world > 1 else model
+    crit = MSELoss()
+    groups = param_groups(model)
+    groups[0]["weight_decay"] = 0.05                                   # main_videomae_pretrain.py --wd default
+    opt = (torch.optim.AdamW(groups, lr=1.5e-4, betas=(0.9, 0.95), fused=True) if args.torch_optimizer
+           else FusedAdamW(groups, lr=1.5e-4, betas=(0.9, 0.95), eps=1e-8))
+    gen = TubeMaskingGeneratorGPU(B, (8, 14, 14), 0.9, device=dev)
+    host = []
+    for i in range(2):
+        g = torch.Generator().manual_seed(1234 + rank + 1000 * i)
+        host.append(torch.randint(0, 256, (B, 16, 224, 224, 3), dtype=torch.uint8, generator=g).pin_memory())
+    resident = [c.to(dev) for c in host]
+    h2d_bytes = host[0].numel() + B * 1568                             # clips + the bool mask made on the host by the generator
+
+    def step(clips):
+        opt.zero_grad(set_to_none=True)
+        mask = gen()                                                   # :319 (host RNG + argsort, copied to the device)
+        out, tgt = net(clips, mask, return_targets=True)
+        loss = crit(out, tgt)
+        loss.backward()
+        opt.step()
+        return loss
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t)
+
+    for i in range(args.warmup):
+        loss = step(resident[i % 2])
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    ops.TIMED = {}
+    launches0 = _lib.launch_count
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.steps):
+        loss = step(resident[i % 2])
+    e1.record()
+    barrier()
+    launches = _lib.launch_count - launches0
+    timed, ops.TIMED = ops.TIMED, None
+    ms_step = max_over_ranks(e0.elapsed_time(e1)) / args.steps
+    clocks = sampler.stop() if rank == 0 else None
+    loss_val = float(loss)
+    value = world * B / (ms_step / 1e3)
+
+    # end to end: pinned uint8 clips copied H2D every step (double-buffered on a copy stream), loss read back
+    copy_stream = torch.cuda.Stream(dev)
+    dbuf = [torch.empty_like(c, device=dev) for c in host]
+    ready, consumed = [torch.cuda.Event(), torch.cuda.Event()], [torch.cuda.Event(), torch.cuda.Event()]
+
+    def prefetch(i):
+        s = i % 2
+        with torch.cuda.stream(copy_stream):
+            copy_stream.wait_event(consumed[s])
+            dbuf[s].copy_(host[s], non_blocking=True)
+            ready[s].record(copy_stream)
+
+    for s in range(2):
+        consumed[s].record()
+    barrier()
+    e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e2.record()
+    prefetch(0)
+    for i in range(args.steps):
+        if i + 1 < args.steps:
+            prefetch(i + 1)
+        torch.cuda.current_stream().wait_event(ready[i % 2])
+        loss = step(dbuf[i % 2])
+        consumed[i % 2].record()
+        _ = loss.item()
+    e3.record()
+    barrier()
+    ms_e2e = max_over_ranks(e2.elapsed_time(e3)) / args.steps
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    pk = peaks()
+    fam = []
+    for name, evs in timed.items():
+        ms = sum(s.elapsed_time(e) for s, e, _ in evs) / args.steps
+        work = sum(w for _, _, w in evs) / args.steps
+        tensor = name.startswith("gemm") or name.startswith("attn")
+        ach = work / (ms * 1e-3) / (1e12 if tensor else 1e9) if ms > 0 else 0.0
+        peak = pk["tf_sust"] if tensor else pk["hbm"]
+        fam.append({"kernel": name, "launches_per_step": len(evs) / args.steps, "ms_per_step": ms, "share_of_step": ms / ms_step,
+                    "bound": "tensor" if tensor else "hbm", "achieved": ach, "unit": "TFLOP/s" if tensor else "GB/s",
+                    "peak": peak, "frac": ach / peak})
+    fam.sort(key=lambda d: -d["ms_per_step"])
+    top = fam[0]
+    roofline = {"kernel": top["kernel"], "bound": top["bound"], "achieved": top["achieved"], "peak": top["peak"], "unit": top["unit"],
+                "frac": top["frac"], "traffic": None, "peak_source": pk["source"] + " (sustained: timed inside the step)"}
+    step_tf = 3 * FWD_GFLOP_PER_PAIR["videomae_16f"] * 1e9 * B / (ms_step * 1e-3) / 1e12
+    cpu_baseline = None
+    if world == 1 and not args.no_cpu_baseline:
+        threads = os.cpu_count() or 1
+        v, ms = cpu_reference_videomae_clips_per_s(4, 1, 0, threads)
+        cpu_baseline = {"value": v, "unit": "clips/s", "cores": threads, "kind": "port",
+                        "sample": f"oracle port (fp32 PyTorch restatement), 4 clips, one targets+fwd+MSE+bwd+AdamW step, no warm-up "
+                                  f"({ms / 1e3:.1f} s)"}
+    line = {"metric": "clips/sec VideoMAE ViT-B/16 16f pretrain step", "value": value, "unit": "clips/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": f"VideoMAE ViT-B/16 16f 224^2 pretrain step, 90% tube masking, 4-layer decoder, {B} clips/GPU "
+                                   "(BASELINE.json configs[4])", "clips_per_gpu": B, "global_batch": world * B,
+                       "optimizer": "AdamW (torch fused)" if args.torch_optimizer else "AdamW (avion_b200 multi-tensor kernel)",
+                       "parallelism": f"dp{world}", "l2": f"inputs_exceed_l2 ({host[0].numel() / 1e6:.0f} MB uint8 clips per step)"},
+            "loss": loss_val, "gpu_launches": launches,
+            "e2e": {"value": world * B / (ms_e2e / 1e3), "unit": "clips/s", "ms_per_step": ms_e2e, "h2d_bytes_per_step": h2d_bytes,
+                    "d2h_bytes_per_step": 4},
+            "clocks": clocks, "roofline": roofline, "kernels": fam[:12],
+            "step_tensor": {"algorithmic_tflops": step_tf, "peak": pk["tf_sust"], "frac": step_tf / pk["tf_sust"]},
+            "cpu_baseline": cpu_baseline}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=4)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--batch", type=int, default=256, help="clips per GPU")
+    ap.add_argument("--batch", type=int, default=None, help="clips per GPU (default 256; 64 for vitl14 / videomae)")
     ap.add_argument("--frames", type=int, default=16)
-    ap.add_argument("--model", default="vitb16", choices=["vitb16", "vitl14"], help="vitl14: BASELINE.json configs[3], use --batch 64")
+    ap.add_argument("--model", default="vitb16", choices=["vitb16", "vitl14", "videomae"],
+                    help="vitl14: BASELINE.json configs[3]; videomae: configs[4] (both default to 64 clips/GPU)")
     ap.add_argument("--cpu-pairs", type=int, default=2)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--torch-optimizer", action="store_true", help="torch.optim.AdamW(fused=True) instead of avion_b200.optim.FusedAdamW")
     args = ap.parse_args()
+    if args.batch is None:
+        args.batch = 256 if args.model == "vitb16" else 64
     if args.impl == "reference":
         run_reference(args)
     else:

@@ -147,6 +147,35 @@ int avn_adamw_step(void* const* params, const void* const* grads, void* const* e
 /* logit_scale.data.clamp_(0, 4.6052) (main_lavila_pretrain.py:880) without a host round trip */
 int avn_clamp_scalar_f32(float* x, float lo, float hi, avn_stream_t stream);
 
+/* ---- VideoMAE pretraining step (BASELINE.json configs[4]) ---------------------------------------
+ * The encoder / decoder blocks use avn_layernorm_*, avn_gemm_bf16 and avn_attn_* above; these are the pieces around them.
+ *
+ * avn_tube_mask_slots: mask uint8/bool [B,N] (1 = masked; TubeMaskingGeneratorGPU, avion/data/transforms.py:279-302) ->
+ * slot int32 [B,N] = position of token n in "visible ascending, then masked ascending" (the order of x[~mask] followed by
+ * expand_pos_embed[mask], avion/models/model_videomae.py:383,575-577), order int32 [B,N] = its inverse, counts int32 [B]
+ * = visible tokens per clip (may be NULL). */
+int avn_tube_mask_slots(const uint8_t* mask, int32_t* slot, int32_t* order, int32_t* counts, int B, int N,
+                        avn_stream_t stream);
+/* frames uint8 [B,T,crop,crop,3] (decord layout, fused decode-crop output) ->
+ *   patches bf16 [B,n_visible,3*2*p*p]: (x-mean)/std, feature order (c p0 p1 p2) of PatchEmbed (model_videomae.py:161) /
+ *     Conv3d weight flattening (:153-155), rows in slot order, VISIBLE tokens only;
+ *   targets fp32 [B,N-n_visible,3*2*p*p]: raw pixels standardised per patch and channel with the unbiased variance and
+ *     eps 1e-6 on the std, feature order (p0 p1 p2 c) (scripts/main_videomae_pretrain.py:322-334), MASKED tokens only.
+ * Either output may be NULL.  1 B read per input element; 2 B written per visible, 4 B per masked element. */
+int avn_tubelet_transform_u8(const uint8_t* frames, const int32_t* slot, void* patches, float* targets, int B, int T,
+                             int crop, int patch, int n_visible, const float* mean3, const float* std3, avn_stream_t stream);
+/* out bf16 [B,n,D] = table[idx[b*idx_stride + j]] (+ add_row on rows j >= add_from when add_row != NULL): sinusoid position
+ * rows in token order, mask_token added on the masked rows (model_videomae.py:379,574-577) */
+int avn_gather_rows_f32_bf16(const float* table, const int32_t* idx, int64_t idx_stride, const float* add_row, int add_from,
+                             void* out, int B, int n, int D, avn_stream_t stream);
+/* out[c] (fp32) += sum over b < B, r < rows of x[b*batch_stride + r*cols + c] (bf16): d(mask_token) */
+int avn_colsum_batched_bf16(const void* x, int B, int64_t batch_stride, int rows, int cols, float* out, avn_stream_t stream);
+/* torch.nn.MSELoss() (scripts/main_videomae_pretrain.py:129,341): loss[0] = mean((pred - target)^2), pred bf16, target fp32,
+ * deterministic two-stage sum (workspace: avn_mse_workspace_floats() floats); bwd: dpred = 2/n * gloss[0] * (pred - target). */
+int avn_mse_workspace_floats(void);
+int avn_mse_fwd(const void* pred, const float* target, int64_t n, float* workspace, float* loss, avn_stream_t stream);
+int avn_mse_bwd(const void* pred, const float* target, const float* gloss, int64_t n, void* dpred, avn_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

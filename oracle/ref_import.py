@@ -62,3 +62,28 @@ def build_reference_clip(cfg, sd):
     missing, unexpected = model.load_state_dict({to_reference_key(k): v for k, v in sd.items()}, strict=True)
     assert not missing and not unexpected
     return model.float()
+
+
+def import_reference_videomae():
+    """avion/models/model_videomae.py unmodified (adds the `drop_path` symbol it imports from timm; rates are 0)."""
+    import_reference()
+    layers = sys.modules["timm.models.layers"]
+    if not hasattr(layers, "drop_path"):
+        layers.drop_path = lambda x, drop_prob=0., training=False: x
+    from avion.models import model_videomae
+    return model_videomae
+
+
+def build_reference_videomae(cfg, sd):
+    """Reference PretrainVisionTransformer with the VIDEOMAE_VITB16 literals (model_videomae.py:583-596) scaled to cfg."""
+    from functools import partial
+    M = import_reference_videomae()
+    assert cfg.frames == 16, "the reference's PatchEmbed hard-codes num_frames=16 (model_videomae.py:142,322-325)"
+    model = M.PretrainVisionTransformer(
+        img_size=cfg.image_size, patch_size=cfg.patch, encoder_embed_dim=cfg.enc_dim, encoder_depth=cfg.enc_depth,
+        encoder_num_heads=cfg.enc_heads, encoder_num_classes=0, decoder_num_classes=cfg.feats, decoder_embed_dim=cfg.dec_dim,
+        decoder_num_heads=cfg.dec_heads, decoder_depth=cfg.dec_depth, mlp_ratio=4, qkv_bias=True,
+        norm_layer=partial(torch.nn.LayerNorm, eps=1e-6))
+    missing, unexpected = model.load_state_dict(sd, strict=True)
+    assert not missing and not unexpected
+    return model.float()
