@@ -408,14 +408,22 @@ def run_videomae(args, world, rank, local_rank, dev):
     resident = [c.to(dev) for c in host]
     h2d_bytes = host[0].numel() + B * 1568                             # clips + the bool mask made on the host by the generator
 
-    def step(clips):
+    def fwd_bwd(clips, mask):
         opt.zero_grad(set_to_none=True)
-        mask = gen()                                                   # :319 (host RNG + argsort, copied to the device)
         out, tgt = net(clips, mask, return_targets=True)
         loss = crit(out, tgt)
         loss.backward()
+        return loss.detach()
+
+    def eager_step(clips):
+        mask = gen()                                                   # :319 (host RNG + argsort, copied to the device)
+        loss = fwd_bwd(clips, mask)
         opt.step()
         return loss
+
+    # One process, no DDP hooks: replay zero_grad+forward+loss+backward as ONE CUDA graph (the eager step is bound by the
+    # ~1800 Python/ctypes launches, not by the GPU); the mask (host RNG) and the optimizer step stay outside the graph.
+    use_graph = world == 1 and not args.no_graph
 
     def barrier():
         if world > 1:
@@ -430,21 +438,39 @@ def run_videomae(args, world, rank, local_rank, dev):
         return float(t)
 
     for i in range(args.warmup):
-        loss = step(resident[i % 2])
+        eager_step(resident[i % 2])
     barrier()
+    # per-family device time: an EAGER pass (events cannot be timed inside a graph replay); kernel durations do not depend on
+    # how the kernels were launched.  Also counts the launches of one step.
+    ops.TIMED = {}
+    launches0 = _lib.launch_count
+    for i in range(args.steps):
+        eager_step(resident[i % 2])
+    barrier()
+    launches = _lib.launch_count - launches0
+    timed, ops.TIMED = ops.TIMED, None
+    if use_graph:          # capture AFTER the eager passes: from here on p.grad are the graph's static gradient buffers
+        from avion_b200.graph import GraphedStep
+        graphed = GraphedStep(fwd_bwd, [resident[0], gen()])
+
+        def step(clips):
+            loss = graphed(clips, gen())
+            opt.step()
+            return loss
+        for i in range(args.warmup):
+            step(resident[i % 2])
+        barrier()
+    else:
+        step = eager_step
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
-    ops.TIMED = {}
-    launches0 = _lib.launch_count
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for i in range(args.steps):
         loss = step(resident[i % 2])
     e1.record()
     barrier()
-    launches = _lib.launch_count - launches0
-    timed, ops.TIMED = ops.TIMED, None
     ms_step = max_over_ranks(e0.elapsed_time(e1)) / args.steps
     clocks = sampler.stop() if rank == 0 else None
     loss_val = float(loss)
@@ -511,7 +537,8 @@ def run_videomae(args, world, rank, local_rank, dev):
             "config": {"workload": f"VideoMAE ViT-B/16 16f 224^2 pretrain step, 90% tube masking, 4-layer decoder, {B} clips/GPU "
                                    "(BASELINE.json configs[4])", "clips_per_gpu": B, "global_batch": world * B,
                        "optimizer": "AdamW (torch fused)" if args.torch_optimizer else "AdamW (avion_b200 multi-tensor kernel)",
-                       "parallelism": f"dp{world}", "l2": f"inputs_exceed_l2 ({host[0].numel() / 1e6:.0f} MB uint8 clips per step)"},
+                       "parallelism": f"dp{world}", "launch": "cuda_graph(zero_grad+fwd+loss+bwd) + eager mask/optimizer" if use_graph else "eager",
+                       "l2": f"inputs_exceed_l2 ({host[0].numel() / 1e6:.0f} MB uint8 clips per step)"},
             "loss": loss_val, "gpu_launches": launches,
             "e2e": {"value": world * B / (ms_e2e / 1e3), "unit": "clips/s", "ms_per_step": ms_e2e, "h2d_bytes_per_step": h2d_bytes,
                     "d2h_bytes_per_step": 4},
@@ -535,6 +562,7 @@ def main():
                     help="vitl14: BASELINE.json configs[3]; videomae: configs[4] (both default to 64 clips/GPU)")
     ap.add_argument("--cpu-pairs", type=int, default=2)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="videomae: launch the step eagerly instead of replaying a CUDA graph")
     ap.add_argument("--torch-optimizer", action="store_true", help="torch.optim.AdamW(fused=True) instead of avion_b200.optim.FusedAdamW")
     args = ap.parse_args()
     if args.batch is None:

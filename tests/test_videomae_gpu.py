@@ -203,3 +203,41 @@ def test_full_size_forward_backward_properties():
         model.mask_token += eps
         l1 = float(MSELoss()(model.forward_with_targets(clips, mask)[0], tgt))
     assert l1 > l0                                         # stepping along +grad increases the loss
+
+
+def test_graphed_step_matches_eager():
+    """avion_b200.graph.GraphedStep: one CUDA-graph replay of zero_grad+forward+loss+backward gives the eager step's loss and
+    gradients (split-K reductions are order-dependent, hence allclose), follows new inputs, and feeds FusedAdamW."""
+    from avion_b200.graph import GraphedStep
+    from avion_b200.losses import MSELoss
+    from avion_b200.optim import FusedAdamW
+    cfg = O.TINY
+    model = build(cfg)
+    model.load_state_dict(O.make_state_dict(cfg, 0), strict=True)
+    crit = MSELoss()
+    opt = FusedAdamW(model.parameters(), lr=1e-3)
+    batches = [tuple(t.cuda() for t in O.make_inputs(cfg, 4, s)) for s in (1, 2)]
+
+    def fwd_bwd(clips, mask):
+        opt.zero_grad(set_to_none=True)
+        out, tgt = model(clips, mask, return_targets=True)
+        loss = crit(out, tgt)
+        loss.backward()
+        return loss.detach()
+
+    eager = []
+    for clips, mask in batches:
+        loss = fwd_bwd(clips, mask)
+        eager.append((float(loss), {k: p.grad.clone() for k, p in model.named_parameters()}))
+    step = GraphedStep(fwd_bwd, list(batches[0]))
+    for (clips, mask), (l_ref, g_ref) in zip(batches, eager):
+        loss = step(clips, mask)
+        assert abs(float(loss) - l_ref) <= 1e-5 * abs(l_ref)
+        for k, p in model.named_parameters():
+            assert torch.allclose(p.grad, g_ref[k], rtol=1e-3, atol=1e-5 * float(g_ref[k].abs().max()) + 1e-12), k
+    before = model.mask_token.detach().clone()
+    losses = []
+    for _ in range(8):
+        losses.append(float(step(*batches[0])))
+        opt.step()
+    assert not torch.equal(before, model.mask_token.detach()) and losses[-1] < losses[0], losses
