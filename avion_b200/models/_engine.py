@@ -156,5 +156,19 @@ def cast_layers(layer_params):
     return out
 
 
+def zeros_f32_like_many(tensors):
+    """One zero-filled fp32 allocation (one memset instead of one fill kernel per gradient tensor) carved into views shaped like
+    `tensors`; every view starts on a 16-byte boundary (TMA reduce-add target of the wgrad GEMM)."""
+    sizes = [(t.numel() + 3) // 4 * 4 for t in tensors]
+    flat = torch.zeros(sum(sizes), dtype=f32, device=tensors[0].device)
+    out, off = [], 0
+    for t, n in zip(tensors, sizes):
+        out.append(flat[off:off + t.numel()].view(t.shape))
+        off += n
+    return out
+
+
 def zero_grads(layer_params):
-    return [{k: _zeros_like_f32(P[k]) for k in BLOCK_KEYS} for P in layer_params]
+    flat = zeros_f32_like_many([P[k] for P in layer_params for k in BLOCK_KEYS])
+    n = len(BLOCK_KEYS)
+    return [dict(zip(BLOCK_KEYS, flat[i * n:(i + 1) * n])) for i in range(len(layer_params))]

@@ -171,9 +171,8 @@ class _VideoMAEFn(torch.autograd.Function):
         dout = dout.to(bf16).contiguous()
         layers = ctx.layers
         grads = E.zero_grads(_unflatten(flat))
-        z = E._zeros_like_f32
-        g_pe_w, g_pe_b, g_encn_w, g_encn_b, g_e2d = z(pe_w), z(pe_b), z(encn_w), z(encn_b), z(e2d_w)
-        g_mask, g_decn_w, g_decn_b, g_head_w, g_head_b = z(mask_token), z(decn_w), z(decn_b), z(head_w), z(head_b)
+        (g_pe_w, g_pe_b, g_encn_w, g_encn_b, g_e2d, g_mask, g_decn_w, g_decn_b, g_head_w, g_head_b) = E.zeros_f32_like_many(
+            [pe_w, pe_b, encn_w, encn_b, e2d_w, mask_token, decn_w, decn_b, head_w, head_b])
         # ---- head
         ops.colsum(dout, g_head_b)
         ops.gemm(GEMM_TN, EPI_F32_ADD, Fo, Dd, Nm, dout, Fo, yn[:, Nv:], Dd, g_head_w, Dd, batch=B, a_bs=Nm * Fo, b_bs=N * Dd,

@@ -35,6 +35,34 @@ def run():
     assert cos_i >= 0.999 and cos_t >= 0.999, "embedding cosine below 0.999"
     assert rel < 1e-3 * 5, "loss deviates from the oracle"
     assert gn > 0 and gn == gn
+    run_videomae()
+
+
+def run_videomae():
+    """One tiny VideoMAE pretraining step (BASELINE.json configs[4]) on cuda:0, checked against the CPU oracle."""
+    from functools import partial
+    from oracle import videomae_oracle as V        # checker only
+    from avion_b200.losses import MSELoss
+    from avion_b200.models.model_videomae import PretrainVisionTransformer
+    cfg = V.TINY
+    sd = V.make_state_dict(cfg, 0)
+    clips, mask = V.make_inputs(cfg, 4, 1234)
+    model = PretrainVisionTransformer(
+        img_size=cfg.image_size, patch_size=cfg.patch, encoder_embed_dim=cfg.enc_dim, encoder_depth=cfg.enc_depth,
+        encoder_num_heads=cfg.enc_heads, decoder_num_classes=cfg.feats, decoder_embed_dim=cfg.dec_dim,
+        decoder_num_heads=cfg.dec_heads, decoder_depth=cfg.dec_depth, mlp_ratio=4, qkv_bias=True,
+        norm_layer=partial(torch.nn.LayerNorm, eps=1e-6), num_frames=cfg.frames).cuda()
+    model.load_state_dict(sd, strict=True)
+    out, tgt = model(clips.cuda(), mask.cuda(), return_targets=True)
+    loss = MSELoss()(out, tgt)
+    loss.backward()
+    torch.cuda.synchronize()
+    ref = V.train_step_forward(sd, clips, mask, cfg)
+    cos = torch.nn.functional.cosine_similarity(out.detach().float().cpu(), ref["outputs"], dim=-1).min().item()
+    rel = abs(loss.item() - ref["loss"].item()) / abs(ref["loss"].item())
+    terr = (tgt.cpu() - ref["targets"]).abs().max().item()
+    print(f"smoke videomae: loss={loss.item():.5f} oracle={ref['loss'].item():.5f} rel={rel:.2e} cos_pred={cos:.5f} target_err={terr:.1e}")
+    assert cos >= 0.999 and rel < 1e-3 and terr <= 2e-5
 
 
 def build_model(cfg):

@@ -61,3 +61,51 @@ def test_ops_refuse_cpu_tensors(built):
     g = torch.ones(128)
     with pytest.raises(RuntimeError, match="CUDA"):
         ops.layernorm_fwd(x, g, g, 1e-6)
+
+
+def _fake_open_clip_sd(layers=2, width=16, t_width=8, ctx=5, vocab=11, prefix=""):
+    import torch
+    g = torch.Generator().manual_seed(0)
+    r = lambda *s: torch.randn(*s, generator=g)      # noqa: E731
+    sd = {"logit_scale": r(()), "visual.proj": r(width, 4), "positional_embedding": r(ctx, t_width), "text_projection": r(t_width, 4),
+          "token_embedding.weight": r(vocab, t_width), "ln_final.weight": r(t_width), "ln_final.bias": r(t_width),
+          "visual.conv1.weight": r(width, 3, 2, 2), "visual.class_embedding": r(width), "visual.positional_embedding": r(5, width),
+          "visual.ln_pre.weight": r(width)}
+    for i in range(layers):
+        for n, shape in (("attn.in_proj_weight", (3 * width, width)), ("attn.in_proj_bias", (3 * width,)),
+                         ("attn.out_proj.weight", (width, width)), ("attn.out_proj.bias", (width,)), ("ln_1.weight", (width,)),
+                         ("ln_1.bias", (width,)), ("ln_2.weight", (width,)), ("ln_2.bias", (width,)),
+                         ("mlp.c_fc.weight", (4 * width, width)), ("mlp.c_fc.bias", (4 * width,)),
+                         ("mlp.c_proj.weight", (width, 4 * width)), ("mlp.c_proj.bias", (width,))):
+            sd[f"visual.transformer.resblocks.{i}.{n}"] = r(*shape)
+            sd[f"transformer.resblocks.{i}.{n}"] = r(*[s // 2 for s in shape])
+    return {prefix + k: v for k, v in sd.items()}
+
+
+def test_checkpoint_remap_matches_reference():
+    """avion_b200.models.utils vs avion/models/utils.py on a synthetic OpenCLIP-style state dict (live reference)."""
+    import pytest
+    import torch
+    from oracle import ref_import as R
+    from avion_b200.models import utils as U
+    # properties that hold without the reference
+    out = U.remap_keys_from_open_clip_to_vit({"state_dict": _fake_open_clip_sd(prefix="module.")}, 2, 2, context_length=7,
+                                             vocab_size=13, use_fast_conv1=True, use_flash_attn=True)
+    assert out["visual.conv1.weight"].shape == (16, 12) and out["textual.positional_embedding"].shape == (7, 8)
+    assert out["textual.token_embedding.weight"].shape == (13, 8) and "visual.transformer.resblocks.1.attn.Wqkv.weight" in out
+    assert "visual.image_projection" not in out and "logit_scale" not in out
+    if not R.available():
+        pytest.skip("reference tree only exists in the build container")
+    R.import_reference()
+    from avion.models import utils as RU
+    for kw in (dict(use_fast_conv1=True, use_flash_attn=True, context_length=7, vocab_size=13),
+               dict(use_fast_conv1=False, use_flash_attn=False, context_length=3, vocab_size=11)):
+        a = U.remap_keys_from_open_clip_to_vit(_fake_open_clip_sd(prefix="module."), 2, 2, **kw)
+        b = RU.remap_keys_from_open_clip_to_vit(_fake_open_clip_sd(prefix="module."), 2, 2, **kw)
+        assert list(a) == list(b) and all(torch.equal(a[k], b[k]) for k in a)
+    cur = {"visual.temporal_embedding": torch.zeros(8, 6), "visual.positional_embedding": torch.zeros(5, 6)}
+    for frames, fix in ((8, "bilinear"), (8, "interp"), (2, "bilinear")):
+        new = lambda: {"visual.temporal_embedding": torch.arange(24.).view(4, 6), "visual.positional_embedding": torch.ones(5, 6)}  # noqa: E731
+        a = U.inflate_positional_embeds(cur, new(), num_frames=frames, load_temporal_fix=fix)
+        b = RU.inflate_positional_embeds(cur, new(), num_frames=frames, load_temporal_fix=fix)
+        assert all(torch.equal(a[k], b[k]) for k in b)

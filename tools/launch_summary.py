@@ -1,5 +1,5 @@
 """Aggregate an `ncu --metrics gpu__time_duration.sum --csv` launch list into per-kernel time of ONE train step.
-python tools/launch_summary.py launches.csv [step_index]   (steps are delimited by clip_transform_kernel, one per step)"""
+python tools/launch_summary.py launches.csv [step_index]   (steps are delimited by clip_transform_kernel / tubelet_transform_kernel, one per step)"""
 import collections
 import csv
 import re
@@ -16,7 +16,7 @@ for r in rd:
     unit = r.get("Metric Unit", "ns")
     ns = v * {"ns": 1.0, "us": 1e3, "ms": 1e6, "s": 1e9}.get(unit, 1.0)
     rows.append((r["Kernel Name"], ns))
-starts = [i for i, (k, _) in enumerate(rows) if "clip_transform_kernel" in k]
+starts = [i for i, (k, _) in enumerate(rows) if "clip_transform_kernel" in k or "tubelet_transform_kernel" in k]
 which = int(sys.argv[2]) if len(sys.argv) > 2 else len(starts) - 2
 lo, hi = starts[which], (starts[which + 1] if which + 1 < len(starts) else len(rows))
 step = rows[lo:hi]
