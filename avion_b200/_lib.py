@@ -57,12 +57,16 @@ SIGNATURES = {
     "avn_mse_workspace_floats": [],
     "avn_mse_fwd": [_vp, _vp, _i64, _vp, _vp, _vp],
     "avn_mse_bwd": [_vp, _vp, _vp, _i64, _vp, _vp],
+    "avn_mmr_workspace_floats": [_i, _i],
+    "avn_mmr_fwd": [_vp, _vp, _i, _i, _f, _i, _vp, _vp, _vp],
+    "avn_mmr_bwd": [_vp, _vp, _i, _i, _f, _i, _vp, _vp, _vp],
 }
 
 # kernels launched per C-ABI call (for the bench's gpu_launches count); default 1
 KERNELS_PER_CALL = {"avn_attn_bwd": 3, "avn_infonce_bwd": 3, "avn_head_bwd": 2, "avn_pos_table_bwd": 2,
                     "avn_token_embed_bwd": 2, "avn_sample_rrc_boxes": 0, "avn_device_check": 0, "avn_version": 0,
-                    "avn_adamw_chunk_elems": 0, "avn_mse_workspace_floats": 0, "avn_mse_fwd": 2}
+                    "avn_adamw_chunk_elems": 0, "avn_mse_workspace_floats": 0, "avn_mse_fwd": 2,
+                    "avn_mmr_workspace_floats": 0, "avn_mmr_fwd": 3}
 launch_count = 0
 
 _lib = None

@@ -6,7 +6,7 @@ from concurrent.futures import ThreadPoolExecutor
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CU = ["api.cu", "gemm.cu", "attention_fwd.cu", "attention_bwd.cu", "transform.cu", "layernorm.cu", "elementwise.cu",
-      "head.cu", "infonce.cu", "optim.cu", "videomae.cu"]
+      "head.cu", "infonce.cu", "optim.cu", "videomae.cu", "ranking.cu"]
 CPP = ["rrc.cpp"]
 LIB = os.path.join(HERE, "libavion_b200.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")

@@ -1,1 +1,1 @@
-from .losses import ClipLoss, MSELoss  # noqa: F401
+from .losses import ClipLoss, MaxMarginRankingLoss, MSELoss  # noqa: F401

@@ -88,3 +88,52 @@ class MSELoss(nn.Module):
 
     def forward(self, input, target):
         return _MSEFn.apply(input.contiguous(), target.contiguous())
+
+
+class _MaxMarginFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, img, txt, margin, fix_norm, rank, world, local_loss, gather_with_grad, group):
+        img32, txt32 = img.detach().float().contiguous(), txt.detach().float().contiguous()
+        n, E = img32.shape
+        if world > 1:
+            both = _dist.gather_packed(img32, txt32, world, group)
+            all_img, all_txt = both[0], both[1]
+        else:
+            all_img, all_txt = img32, txt32
+        loss, ws = ops.mmr_fwd(all_txt, all_img, margin, fix_norm)
+        ctx.save_for_backward(ws)
+        ctx.cfg = (margin, fix_norm, rank, world, local_loss, gather_with_grad, group, n, E, img.dtype, txt.dtype)
+        return loss
+
+    @staticmethod
+    def backward(ctx, gloss):
+        (ws,) = ctx.saved_tensors
+        margin, fix_norm, rank, world, local_loss, gather_with_grad, group, n, E, dt_i, dt_t = ctx.cfg
+        dtxt, dimg = ops.mmr_bwd(ws, gloss.float().reshape(1).contiguous(), n * world, E, margin, fix_norm)
+        if world > 1 and gather_with_grad:
+            # torch.distributed.nn.all_gather backward: every rank's loss sends gradient to every rank's features (:55-60)
+            local = _dist.scatter_sum(torch.stack([dimg, dtxt]), world, group)
+            dimg, dtxt = local[0], local[1]
+        elif world > 1:
+            if local_loss:                        # gathered copies carry no gradient and the local slice is not re-inserted (:61-72)
+                return (torch.zeros_like(dimg[:n]).to(dt_i), torch.zeros_like(dtxt[:n]).to(dt_t)) + (None,) * 7
+            dimg, dtxt = dimg[rank * n:(rank + 1) * n], dtxt[rank * n:(rank + 1) * n]
+        return (dimg.to(dt_i), dtxt.to(dt_t), None, None, None, None, None, None, None)
+
+
+class MaxMarginRankingLoss(nn.Module):
+    """avion/losses/losses.py:163-227 (EK-100 multi-instance retrieval fine-tuning): same constructor and result dict; the loss
+    over the all-gathered features is evaluated by the `avn_mmr_*` kernels without materialising the similarity matrix."""
+
+    def __init__(self, margin=0.2, fix_norm=True, local_loss=False, gather_with_grad=False, rank=0, world_size=1,
+                 use_horovod=False, group=None):
+        super().__init__()
+        assert not use_horovod, "horovod is not supported"
+        self.fix_norm, self.margin = fix_norm, margin
+        self.local_loss, self.gather_with_grad = local_loss, gather_with_grad
+        self.rank, self.world_size, self.group = rank, world_size, group
+
+    def forward(self, image_features, text_features, weight=None):
+        loss = _MaxMarginFn.apply(image_features, text_features, self.margin, self.fix_norm, self.rank, self.world_size,
+                                  self.local_loss, self.gather_with_grad, self.group)
+        return {"loss": loss, "max_margin_loss": loss}

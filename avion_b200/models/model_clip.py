@@ -6,6 +6,65 @@ import torch.nn as nn
 from .transformer import TextTransformer, VisionTransformer
 
 
+class _DenseFn(torch.autograd.Function):
+    """y = x @ w^T + b on the tcgen05 GEMM for a small classifier head: x [n,K] (any float dtype), w fp32 [N,K], b fp32 [N].
+    N (3806 EK-100 action classes, 97 verbs, 300 nouns) is padded to a multiple of 8 in the bf16 operand copies."""
+
+    @staticmethod
+    def forward(ctx, x, w, b):
+        from .. import ops
+        n, K = x.shape
+        N = w.shape[0]
+        Np = (N + 7) // 8 * 8
+        dev = x.device
+        xb = x.detach().to(torch.bfloat16).contiguous()
+        wb = torch.zeros(Np, K, dtype=torch.bfloat16, device=dev)
+        ops.cast_bf16(w.detach().contiguous(), out=wb[:N])
+        bp = torch.zeros(Np, dtype=torch.float32, device=dev)
+        bp[:N] = b.detach()
+        y = ops.linear_fwd(xb, wb, bp, ops.EPI_BIAS)
+        ctx.save_for_backward(xb, wb)
+        ctx.dims = (N, Np, x.dtype)
+        return y[:, :N].float()
+
+    @staticmethod
+    def backward(ctx, dy):
+        from .. import ops
+        xb, wb = ctx.saved_tensors
+        N, Np, xdtype = ctx.dims
+        n, K = xb.shape
+        dyb = torch.zeros(n, Np, dtype=torch.bfloat16, device=xb.device)
+        dyb[:, :N] = dy
+        dw = torch.zeros(Np, K, dtype=torch.float32, device=xb.device)
+        db = torch.zeros(Np, dtype=torch.float32, device=xb.device)
+        ops.linear_wgrad(dyb, xb, dw)
+        ops.colsum(dyb, db)
+        dx = ops.linear_dgrad(dyb, wb)
+        return dx.to(xdtype), dw[:N], db[:N]
+
+
+class VideoClassifier(nn.Module):
+    """avion/models/model_clip.py:15-38: video tower without its projection -> dropout -> fc_cls (the fine-tune model of
+    scripts/main_lavila_finetune_cls.py).  Same attribute names / state_dict keys (`visual.*`, `fc_cls.weight`, `fc_cls.bias`)."""
+
+    def __init__(self, vision_model: nn.Module, dropout: float, num_classes: int, **kwargs):
+        super().__init__()
+        self.visual = vision_model
+        self.dropout = nn.Dropout(dropout)
+        if hasattr(self.visual, "image_projection"):
+            self.visual.image_projection = None
+        self.fc_cls = nn.Linear(vision_model.width, num_classes, bias=True)     # parameter holder; the GEMM is ours
+        self.fc_cls.weight.data.normal_(mean=0.0, std=0.01)
+        self.fc_cls.bias.data.zero_()
+
+    def forward(self, image):
+        image_embed = self.visual(image)
+        if isinstance(image_embed, list):
+            assert len(image_embed) == 1
+            image_embed = image_embed[0]
+        return _DenseFn.apply(self.dropout(image_embed), self.fc_cls.weight, self.fc_cls.bias)
+
+
 class CLIP(nn.Module):
     """avion/models/model_clip.py:41-99.  forward(image, text) -> (image_embed, text_embed, logit_scale.exp()), both
     embeddings L2-normalised.  `image` may be uint8 clips [B,T,H,W,3] (fused transform entry), bf16 patches, or the

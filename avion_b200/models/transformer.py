@@ -223,6 +223,7 @@ class VisionTransformer(nn.Module):
         self.image_projection = nn.Parameter(scale * torch.randn(width, output_dim))
         self.mean, self.std = MEAN_OPENAI, STD_OPENAI
         self._ws = E.Workspace()
+        self._eye = None
         self.init_parameters()
 
     def init_parameters(self):                                     # transformer.py:269-287
@@ -237,7 +238,8 @@ class VisionTransformer(nn.Module):
                     nn.init.zeros_(p)
                 else:
                     raise NotImplementedError('Unknown parameters named {}'.format(n))
-        nn.init.normal_(self.image_projection, std=self.width ** -0.5)
+        if self.image_projection is not None:
+            nn.init.normal_(self.image_projection, std=self.width ** -0.5)
 
     def set_grad_checkpointing(self, enable=True):                 # transformer.py:305-307
         self.transformer.grad_checkpointing = enable
@@ -268,7 +270,12 @@ class VisionTransformer(nn.Module):
         meta = (self.num_frames, self.patches_per_frame, self.transformer.heads, self.eps, normalize, self._ws)
         flat = _flatten(self.transformer.layer_params())
         tmp = self.temporal_embedding if self.num_frames > 1 else None
-        return _VisionTowerFn.apply(patches, meta, self.class_embedding, self.positional_embedding, tmp, self.image_projection,
+        proj = self.image_projection
+        if proj is None:      # VideoClassifier drops the projection (model_clip.py:27-28): the head kernel gets an exact identity
+            if self._eye is None or self._eye.device != patches.device:
+                self._eye = torch.eye(self.width, dtype=f32, device=patches.device)
+            proj = self._eye
+        return _VisionTowerFn.apply(patches, meta, self.class_embedding, self.positional_embedding, tmp, proj,
                                     self.conv1.weight, self.ln_pre.weight, self.ln_pre.bias, self.ln_post.weight,
                                     self.ln_post.bias, *flat)
 

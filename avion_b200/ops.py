@@ -357,3 +357,22 @@ def mse_bwd(pred, target, gloss):
     with _timed("mse", pred, 8.0 * pred.numel()):
         _lib.call("avn_mse_bwd", _p(pred), _p(target), _p(gloss), pred.numel(), _p(dpred), _stream(pred))
     return dpred
+
+
+def mmr_fwd(text, image, margin, fix_norm):
+    """MaxMarginRankingLoss forward on fp32 [n,E] features -> (loss 0-dim, workspace for mmr_bwd)."""
+    _chk(text, f32, "text"); _chk(image, f32, "image")
+    assert text.shape == image.shape and text.dim() == 2
+    n, E = text.shape
+    ws = torch.empty(_lib.load().avn_mmr_workspace_floats(n, E), dtype=f32, device=text.device)
+    loss = torch.empty((), dtype=f32, device=text.device)
+    _lib.call("avn_mmr_fwd", _p(text), _p(image), n, E, float(margin), int(bool(fix_norm)), _p(ws), _p(loss), _stream(text))
+    return loss, ws
+
+
+def mmr_bwd(ws, gloss, n, E, margin, fix_norm):
+    _chk(gloss, f32, "gloss")
+    dtext = torch.empty(n, E, dtype=f32, device=ws.device)
+    dimage = torch.empty(n, E, dtype=f32, device=ws.device)
+    _lib.call("avn_mmr_bwd", _p(ws), _p(gloss), n, E, float(margin), int(bool(fix_norm)), _p(dtext), _p(dimage), _stream(ws))
+    return dtext, dimage

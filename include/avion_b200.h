@@ -176,6 +176,18 @@ int avn_mse_workspace_floats(void);
 int avn_mse_fwd(const void* pred, const float* target, int64_t n, float* workspace, float* loss, avn_stream_t stream);
 int avn_mse_bwd(const void* pred, const float* target, const float* gloss, int64_t n, void* dpred, avn_stream_t stream);
 
+/* ---- MaxMarginRankingLoss (avion/losses/losses.py:152-227; EK-100 MIR fine-tuning) ---------------------
+ * text, image fp32 [n,E] = the all-gathered features; x = sim_matrix(text, image) (:152-160, eps 1e-8);
+ * loss[0] = mean over i != j (fix_norm != 0; else over all i, j) of relu(m - x_ii + x_ij) and relu(m - x_ii + x_ji) (:197-225).
+ * fwd fills `workspace` (avn_mmr_workspace_floats(n, E) floats: normalised features, norms, diagonal, row partials), which
+ * bwd reads: dtext, dimage fp32 [n,E] = gloss[0] * dL/d(text, image).  Deterministic; neither x nor dL/dx is materialised.
+ * (Rows with |feature| < eps take the gradient of the unclamped normalisation.) */
+int avn_mmr_workspace_floats(int n, int E);
+int avn_mmr_fwd(const float* text, const float* image, int n, int E, float margin, int fix_norm, float* workspace, float* loss,
+                avn_stream_t stream);
+int avn_mmr_bwd(const float* workspace, const float* gloss, int n, int E, float margin, int fix_norm, float* dtext,
+                float* dimage, avn_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -228,7 +228,23 @@ def vision_forward(sd, image: torch.Tensor, cfg: ClipCfg) -> torch.Tensor:
         x = _block(x, sd, f"{v}transformer.resblocks.{i}.", cfg.heads, 1e-6,
                    ("attn.Wqkv.weight", "attn.Wqkv.bias", "mlp.fc1", "mlp.fc2"))
     x = F.layer_norm(x[:, 0], (D,), sd[v + "ln_post.weight"], sd[v + "ln_post.bias"], 1e-6)
+    if sd.get(v + "image_projection") is None:          # VideoClassifier drops it (model_clip.py:27-28; transformer.py:374)
+        return x
     return x @ sd[v + "image_projection"]
+
+
+def classifier_forward(sd, image: torch.Tensor, cfg: ClipCfg) -> torch.Tensor:
+    """VideoClassifier.forward (avion/models/model_clip.py:33-38) with dropout 0: fc_cls(visual(image)) -> [B, classes].
+    sd holds visual.* (without image_projection), fc_cls.weight, fc_cls.bias."""
+    return F.linear(vision_forward(sd, image, cfg), sd["fc_cls.weight"], sd["fc_cls.bias"])
+
+
+def make_classifier_state_dict(cfg: ClipCfg, num_classes: int, seed: int = 0) -> dict:
+    sd = {k: v for k, v in make_state_dict(cfg, seed).items() if k.startswith("visual.") and k != "visual.image_projection"}
+    rs = np.random.RandomState(seed + 1000)
+    sd["fc_cls.weight"] = torch.from_numpy((rs.standard_normal((num_classes, cfg.width)) * 0.05).astype(np.float32))
+    sd["fc_cls.bias"] = torch.from_numpy((rs.standard_normal(num_classes) * 0.05).astype(np.float32))
+    return sd
 
 
 # --------------------------------------------------------------------------------------------------
