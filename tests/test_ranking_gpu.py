@@ -4,8 +4,17 @@ import numpy as np
 import pytest
 import torch
 
+import os
+
 from oracle import ranking_oracle as O
-from tests.test_oracle_ranking import G, TAGS, case
+
+G = np.load(os.path.join(os.path.dirname(__file__), "golden", "ranking_n12.npz"))
+TAGS = ("a", "b", "c")
+
+
+def case(tag):
+    n, E, seed, fix = (int(v) for v in G[f"{tag}:cfg"])
+    return n, E, seed, bool(fix), float(G[f"{tag}:margin"])
 
 pytestmark = pytest.mark.gpu
 
