@@ -57,10 +57,12 @@ __global__ void tube_mask_slots_kernel(const uint8_t* __restrict__ mask, int32_t
 // each of the gw tokens of that row writes either its patch (visible) or its standardised target (masked).
 constexpr int TUBE = 2;
 
+template <int P>      // patch size as a compile-time constant (index arithmetic becomes shifts); 0 = run-time value
 __global__ void __launch_bounds__(256)
 tubelet_transform_kernel(const uint8_t* __restrict__ frames, const int32_t* __restrict__ slot, __nv_bfloat16* __restrict__ patches,
-                         float* __restrict__ targets, int T, int crop, int p, int Nv, float m0, float m1, float m2, float s0,
+                         float* __restrict__ targets, int T, int crop, int p_rt, int Nv, float m0, float m1, float m2, float s0,
                          float s1, float s2) {
+    const int p = P > 0 ? P : p_rt;
     extern __shared__ uint8_t smem[];
     __nv_bfloat16* lut = (__nv_bfloat16*)smem;                 // [3][256]
     float* stat = (float*)(smem + 3 * 256 * 2);                // [gw][3][2] mean, 1/(std+1e-6)
@@ -90,68 +92,88 @@ tubelet_transform_kernel(const uint8_t* __restrict__ frames, const int32_t* __re
     }
     __syncthreads();
 
-    // per (token, channel) statistics of the masked tokens: one warp each, two passes (sum, then squared deviations)
+    // Statistics of the masked tokens: one warp per token.  A token is TUBE*p rows of p*3 contiguous staged bytes; lanes walk
+    // its 32-bit words (channel of byte t in a row = t % 3, so a word at word index k starts at channel k % 3).
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
-    const int per_tok = TUBE * p * p;                          // 512 positions
+    const int per_tok = TUBE * p * p;                          // 512 positions per channel
+    const int wpr = p * 3 / 4;                                 // words per patch row (12)
+    const int words = TUBE * p * wpr;                          // words per token (384)
     if (targets != nullptr) {
-        for (int job = warp; job < g * 3; job += nwarps) {
-            const int ww = job / 3, c = job % 3;
+        for (int ww = warp; ww < g; ww += nwarps) {
             if (tok_slot[ww] < Nv) continue;
-            float s = 0.f;
-            for (int q = lane; q < per_tok; q += 32) {
-                const int r = q / p, p2 = q % p;
-                s += (float)rows[r * row_bytes + (ww * p + p2) * 3 + c];
+            const uint8_t* base = rows + ww * p * 3;
+            float s[3] = {0.f, 0.f, 0.f};
+            for (int idx = lane; idx < words; idx += 32) {
+                const int r = idx / wpr, k = idx - r * wpr, ph = k % 3;
+                const uint32_t w = *(const uint32_t*)(base + r * row_bytes + 4 * k);
+                const float t0 = (float)((w & 0xffu) + (w >> 24)), t1 = (float)((w >> 8) & 0xffu), t2 = (float)((w >> 16) & 0xffu);
+                if (ph == 0) { s[0] += t0; s[1] += t1; s[2] += t2; }
+                else if (ph == 1) { s[1] += t0; s[2] += t1; s[0] += t2; }
+                else { s[2] += t0; s[0] += t1; s[1] += t2; }
             }
-            s = warp_sum(s);
-            const float mean = s / (float)per_tok;
-            float ss = 0.f;
-            for (int q = lane; q < per_tok; q += 32) {
-                const int r = q / p, p2 = q % p;
-                const float d = (float)rows[r * row_bytes + (ww * p + p2) * 3 + c] - mean;
-                ss = fmaf(d, d, ss);
+            float mean[3];
+#pragma unroll
+            for (int c = 0; c < 3; ++c) mean[c] = warp_sum(s[c]) / (float)per_tok;     // exact: integer sums < 2^24
+            float q[3] = {0.f, 0.f, 0.f};
+            for (int idx = lane; idx < words; idx += 32) {
+                const int r = idx / wpr, k = idx - r * wpr, ph = k % 3;
+                const uint32_t w = *(const uint32_t*)(base + r * row_bytes + 4 * k);
+                const float ma = ph == 0 ? mean[0] : (ph == 1 ? mean[1] : mean[2]);   // channel of bytes 0 and 3
+                const float mb = ph == 0 ? mean[1] : (ph == 1 ? mean[2] : mean[0]);   // byte 1
+                const float mc = ph == 0 ? mean[2] : (ph == 1 ? mean[0] : mean[1]);   // byte 2
+                const float d0 = (float)(w & 0xffu) - ma, d3 = (float)(w >> 24) - ma;
+                const float d1 = (float)((w >> 8) & 0xffu) - mb, d2 = (float)((w >> 16) & 0xffu) - mc;
+                const float qa = fmaf(d0, d0, d3 * d3), qb = d1 * d1, qc = d2 * d2;
+                if (ph == 0) { q[0] += qa; q[1] += qb; q[2] += qc; }
+                else if (ph == 1) { q[1] += qa; q[2] += qb; q[0] += qc; }
+                else { q[2] += qa; q[0] += qb; q[1] += qc; }
             }
-            ss = warp_sum(ss);
-            if (lane == 0) {
-                stat[(ww * 3 + c) * 2 + 0] = mean;
-                stat[(ww * 3 + c) * 2 + 1] = 1.0f / (sqrtf(ss / (float)(per_tok - 1)) + 1e-6f);
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+                const float ss = warp_sum(q[c]);
+                if (lane == 0) {
+                    stat[(ww * 3 + c) * 2 + 0] = mean[c];
+                    stat[(ww * 3 + c) * 2 + 1] = 1.0f / (sqrtf(ss / (float)(per_tok - 1)) + 1e-6f);
+                }
             }
         }
     }
     __syncthreads();
 
-    const int p8 = p / 8;
-    for (int ww = 0; ww < g; ++ww) {
-        const int s = tok_slot[ww];
-        if (s < Nv) {
-            if (patches == nullptr) continue;
-            // feature f = ((c*TUBE + p0)*p + p1)*p + p2, 8 consecutive p2 per 16-byte store
-            __nv_bfloat16* out = patches + ((long long)b * Nv + s) * F;
-            for (int o = threadIdx.x; o < F / 8; o += blockDim.x) {
-                const int c = o / (TUBE * p * p8), r = (o / p8) % (TUBE * p), sw0 = (o % p8) * 8;
-                const uint8_t* src = rows + r * row_bytes + (ww * p + sw0) * 3 + c;
-                const __nv_bfloat16* l = lut + c * 256;
-                __nv_bfloat16 v[8];
+    // visible tokens -> patches: feature f = ((c*TUBE + p0)*p + p1)*p + p2, 8 consecutive p2 per 16-byte store
+    if (patches != nullptr) {
+        const int p8 = p / 8, vec = F / 8;
+        for (int i = threadIdx.x; i < g * vec; i += blockDim.x) {
+            const int ww = i / vec, o = i - ww * vec;
+            const int s = tok_slot[ww];
+            if (s >= Nv) continue;
+            const int c = o / (TUBE * p * p8), r = (o / p8) % (TUBE * p), sw0 = (o % p8) * 8;
+            const uint8_t* src = rows + r * row_bytes + (ww * p + sw0) * 3 + c;
+            const __nv_bfloat16* l = lut + c * 256;
+            __nv_bfloat16 v[8];
 #pragma unroll
-                for (int i = 0; i < 8; ++i) v[i] = l[src[i * 3]];
-                *(uint4*)(out + (long long)o * 8) = *(uint4*)v;
-            }
-        } else {
-            if (targets == nullptr) continue;
-            // feature f = (p0*p*p + p1*p + p2)*3 + c: the staged bytes of a patch row in memory order
-            float* out = targets + ((long long)b * (N - Nv) + (s - Nv)) * F;
+            for (int j = 0; j < 8; ++j) v[j] = l[src[j * 3]];
+            *(uint4*)(patches + ((long long)b * Nv + s) * F + (long long)o * 8) = *(uint4*)v;
+        }
+    }
+    // masked tokens -> targets: feature f = (p0*p*p + p1*p + p2)*3 + c = the staged bytes of the token in memory order, so one
+    // 32-bit word of the staged rows becomes one float4 of the output row
+    if (targets != nullptr) {
+        for (int i = threadIdx.x; i < g * words; i += blockDim.x) {
+            const int ww = i / words, o = i - ww * words;
+            const int s = tok_slot[ww];
+            if (s < Nv) continue;
             const float* st = stat + ww * 6;
-            for (int o = threadIdx.x; o < F / 4; o += blockDim.x) {
-                const int f0 = o * 4;
-                float v[4];
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const int f = f0 + i, q = f / 3, c = f % 3;
-                    const int r = q / p, p2 = q % p;
-                    const float x = (float)rows[r * row_bytes + (ww * p + p2) * 3 + c];
-                    v[i] = (x - st[c * 2]) * st[c * 2 + 1];
-                }
-                *(float4*)(out + f0) = make_float4(v[0], v[1], v[2], v[3]);
-            }
+            const int r = o / wpr, k = o - r * wpr, ph = k % 3;
+            const uint32_t w = *(const uint32_t*)(rows + ww * p * 3 + r * row_bytes + 4 * k);
+            const int ca = ph, cb = ph == 2 ? 0 : ph + 1, cc = ph == 0 ? 2 : ph - 1;      // channels of bytes (0,3), 1, 2
+            const float ma = st[2 * ca], ia = st[2 * ca + 1], mb = st[2 * cb], ib = st[2 * cb + 1], mc = st[2 * cc], ic = st[2 * cc + 1];
+            float4 v;
+            v.x = ((float)(w & 0xffu) - ma) * ia;
+            v.y = ((float)((w >> 8) & 0xffu) - mb) * ib;
+            v.z = ((float)((w >> 16) & 0xffu) - mc) * ic;
+            v.w = ((float)(w >> 24) - ma) * ia;
+            *(float4*)(targets + ((long long)b * (N - Nv) + (s - Nv)) * F + 4 * o) = v;
         }
     }
 }
@@ -282,7 +304,7 @@ extern "C" int avn_tubelet_transform_u8(const uint8_t* frames, const int32_t* sl
     AVN_REQUIRE(n_visible >= 0 && n_visible <= (T / TUBE) * g * g, "tubelet_transform: bad visible count");
     const size_t smem = 3 * 256 * 2 + 64 * 6 * 4 + 64 * 4 + (size_t)TUBE * patch * crop * 3;
     AVN_REQUIRE(smem <= 227 * 1024, "tubelet_transform: crop too wide for shared memory");
-    auto kern = tubelet_transform_kernel;
+    auto kern = patch == 16 ? tubelet_transform_kernel<16> : tubelet_transform_kernel<0>;
     AVN_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     kern<<<B * (T / TUBE) * g, 256, smem, stream>>>(frames, slot, (__nv_bfloat16*)patches, targets, T, crop, patch, n_visible,
                                                     mean3[0], mean3[1], mean3[2], std3[0], std3[1], std3[2]);
