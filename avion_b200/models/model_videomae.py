@@ -294,6 +294,9 @@ class PretrainVisionTransformer(nn.Module):
             assert min(c) == max(c), "every clip must have the same number of visible tokens"
             self._nv = c[0]
             self.check_mask = False                                # tube masks have a fixed ratio: checked on the first call
+        else:
+            # later calls: no host read, but a different visible count must not pass silently (device-side assert)
+            torch._assert_async((counts == self._nv).all())
         Nv = self._nv
         if x.dtype == torch.uint8:
             assert x.dim() == 5 and x.shape[1] == self.num_frames and x.shape[2] == self.img_size

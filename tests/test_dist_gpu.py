@@ -57,3 +57,48 @@ def test_sharded_clip_loss_nccl_world2():
         p.join(timeout=300)
         assert p.exitcode == 0
     assert dict(q.get(timeout=5) for _ in range(world)) == {0: True, 1: True}
+
+
+def _worker_mmr(rank, world, port, n, E, q):
+    """MaxMarginRankingLoss sharded over ranks == the single-process loss on the concatenated batch: default mode gives every
+    rank the full loss and the gradient of its own rows; gather_with_grad sums every rank's contribution (= world x)."""
+    sys.path.insert(0, ROOT)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        from avion_b200.losses import MaxMarginRankingLoss
+        torch.manual_seed(0)
+        N = world * n
+        g_img = torch.randn(N, E).cuda()
+        g_txt = (0.25 * g_img.cpu() + torch.randn(N, E)).cuda()
+        off = rank * n
+        fi, ft = g_img.clone().requires_grad_(True), g_txt.clone().requires_grad_(True)
+        full = MaxMarginRankingLoss(world_size=1)(fi, ft)["loss"]
+        full.backward()
+        ok = True
+        for gwg, factor in ((False, 1.0), (True, float(world))):
+            img = g_img[off:off + n].clone().requires_grad_(True)
+            txt = g_txt[off:off + n].clone().requires_grad_(True)
+            loss = MaxMarginRankingLoss(gather_with_grad=gwg, rank=rank, world_size=world)(img, txt)["loss"]
+            loss.backward()
+            ok = ok and torch.allclose(loss, full, rtol=1e-5) \
+                and torch.allclose(img.grad, factor * fi.grad[off:off + n], rtol=1e-4, atol=1e-7) \
+                and torch.allclose(txt.grad, factor * ft.grad[off:off + n], rtol=1e-4, atol=1e-7)
+        q.put((rank, bool(ok)))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_sharded_max_margin_loss_nccl_world2():
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker_mmr, args=(r, world, 29741, 40, 64, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(timeout=300)
+        assert p.exitcode == 0
+    assert dict(q.get(timeout=5) for _ in range(world)) == {0: True, 1: True}
