@@ -169,7 +169,7 @@ def run_reference(args):
     pairs = args.cpu_pairs
     if args.model == "videomae":
         steps, warmup = min(args.steps, 2), min(args.warmup, 1)
-        n = max(pairs, 24)
+        n = max(pairs, 48)
         v, ms = cpu_reference_videomae_clips_per_s(n, steps, warmup, threads)
         sample = f"{n} clips/step, fp32, targets+fwd+MSE+bwd+AdamW, {steps} timed steps after {warmup} warm-up"
         print(json.dumps({"impl": "reference", "metric": "clips/sec VideoMAE ViT-B/16 16f pretrain step", "value": v, "unit": "clips/s",
@@ -527,9 +527,9 @@ def run_videomae(args, world, rank, local_rank, dev):
     cpu_baseline = None
     if world == 1 and not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
-        v, ms = cpu_reference_videomae_clips_per_s(24, 1, 0, threads)
+        v, ms = cpu_reference_videomae_clips_per_s(48, 1, 0, threads)
         cpu_baseline = {"value": v, "unit": "clips/s", "cores": threads, "kind": "port",
-                        "sample": f"oracle port (fp32 PyTorch restatement), 24 clips, one targets+fwd+MSE+bwd+AdamW step, no warm-up "
+                        "sample": f"oracle port (fp32 PyTorch restatement), 48 clips, one targets+fwd+MSE+bwd+AdamW step, no warm-up "
                                   f"({ms / 1e3:.1f} s)"}
     line = {"metric": "clips/sec VideoMAE ViT-B/16 16f pretrain step", "value": value, "unit": "clips/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
