@@ -414,8 +414,11 @@ int launch_bn(const avn_gemm_desc* d, cudaStream_t stream) {
     const long long tiles256 = (long long)((d->M + 127) / 128) * ((d->N + 255) / 256) * (MODE == AVN_GEMM_TN ? 1 : d->batch);
     // big problems: CTA pairs (cta_group::2) on 256 x 256 tiles; AVN_GEMM_CG=1 forces the single-CTA kernel (A/B comparisons)
     static const int force_cg = getenv("AVN_GEMM_CG") ? atoi(getenv("AVN_GEMM_CG")) : 0;
-    if (d->N % 256 == 0 && (tiles256 >= 2 * avn_num_sms() || MODE == AVN_GEMM_TN)) {
-        const bool pair_ok = (MODE == AVN_GEMM_TN) ? (d->M % 256 == 0) : (tiles256 >= 4 * avn_num_sms());
+    // thresholds in units of the SM count (AVN_GEMM_T256 / AVN_GEMM_TPAIR override them for A/B runs)
+    static const double t256 = getenv("AVN_GEMM_T256") ? atof(getenv("AVN_GEMM_T256")) : 2.0;
+    static const double tpair = getenv("AVN_GEMM_TPAIR") ? atof(getenv("AVN_GEMM_TPAIR")) : 4.0;
+    if (d->N % 256 == 0 && (tiles256 >= t256 * avn_num_sms() || MODE == AVN_GEMM_TN)) {
+        const bool pair_ok = (MODE == AVN_GEMM_TN) ? (d->M % 256 == 0) : (tiles256 >= tpair * avn_num_sms());
         if (force_cg != 1 && pair_ok) return launch<256, MODE, EPI, 2>(d, stream);
         return launch<256, MODE, EPI, 1>(d, stream);
     }

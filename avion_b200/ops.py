@@ -16,6 +16,8 @@ _checked_devices = set()
 # Optional per-family device timing (bench.py): TIMED maps a family name to a list of (start, end) CUDA events recorded
 # on the launching stream around each call; None disables it.
 TIMED = None
+TIMED_BY_EPILOGUE = False      # True: one GEMM family per (mode, epilogue) = per kernel template instantiation
+_EPI_NAMES = ("none", "bias", "bias_gelu", "bias_gelu_dual", "bias_residual", "dgelu", "f32_add")
 
 
 class _timed:
@@ -120,7 +122,10 @@ def gemm(mode, epi, M, N, K, A, lda, B, ldb, Cm, ldc, batch=1, a_bs=0, b_bs=0, c
     d = GemmDesc(mode, epi, M, N, K, batch, A.data_ptr(), lda, a_bs, B.data_ptr(), ldb, b_bs, Cm.data_ptr(), ldc, c_bs,
                  C2.data_ptr() if C2 is not None else None, bias.data_ptr() if bias is not None else None,
                  R.data_ptr() if R is not None else None, ldr, r_bs, splits)
-    with _timed("gemm_%s" % ("nt", "nn", "tn")[mode], A, 2.0 * M * N * K * batch):
+    name = "gemm_%s" % ("nt", "nn", "tn")[mode]
+    if TIMED_BY_EPILOGUE:
+        name += "_" + _EPI_NAMES[epi]
+    with _timed(name, A, 2.0 * M * N * K * batch):
         _lib.call("avn_gemm_bf16", C.byref(d), _stream(A))
 
 

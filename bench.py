@@ -20,6 +20,8 @@ import torch
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+# stdout carries exactly ONE JSON line: NCCL's version / debug banner (printed to stdout by default) goes to stderr
+os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
 
 # algorithmic FLOPs per clip-text pair, forward; train step = 3x (no recompute counted)
 FWD_GFLOP_PER_PAIR = {"vitb16_16f": 905.3, "vitb16_4f": 162.95, "vitl14_16f": 4142.8,
@@ -443,6 +445,7 @@ def run_videomae(args, world, rank, local_rank, dev):
     # per-family device time: an EAGER pass (events cannot be timed inside a graph replay); kernel durations do not depend on
     # how the kernels were launched.  Also counts the launches of one step.
     ops.TIMED = {}
+    ops.TIMED_BY_EPILOGUE = True      # a "kernel" = one template instantiation; the GEMM modes here mix 2-4 epilogues each
     launches0 = _lib.launch_count
     for i in range(args.steps):
         eager_step(resident[i % 2])
@@ -521,8 +524,12 @@ def run_videomae(args, world, rank, local_rank, dev):
                     "peak": peak, "frac": ach / peak})
     fam.sort(key=lambda d: -d["ms_per_step"])
     top = fam[0]
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath):
+        traffic = json.load(open(tpath)).get("videomae:" + top["kernel"])
     roofline = {"kernel": top["kernel"], "bound": top["bound"], "achieved": top["achieved"], "peak": top["peak"], "unit": top["unit"],
-                "frac": top["frac"], "traffic": None, "peak_source": pk["source"] + " (sustained: timed inside the step)"}
+                "frac": top["frac"], "traffic": traffic, "peak_source": pk["source"] + " (sustained: timed inside the step)"}
     step_tf = 3 * FWD_GFLOP_PER_PAIR["videomae_16f"] * 1e9 * B / (ms_step * 1e-3) / 1e12
     cpu_baseline = None
     if world == 1 and not args.no_cpu_baseline:
@@ -542,7 +549,7 @@ def run_videomae(args, world, rank, local_rank, dev):
             "loss": loss_val, "gpu_launches": launches,
             "e2e": {"value": world * B / (ms_e2e / 1e3), "unit": "clips/s", "ms_per_step": ms_e2e, "h2d_bytes_per_step": h2d_bytes,
                     "d2h_bytes_per_step": 4},
-            "clocks": clocks, "roofline": roofline, "kernels": fam[:12],
+            "clocks": clocks, "roofline": roofline, "kernels": fam[:14],
             "step_tensor": {"algorithmic_tflops": step_tf, "peak": pk["tf_sust"], "frac": step_tf / pk["tf_sust"]},
             "cpu_baseline": cpu_baseline}
     print(json.dumps(line), flush=True)
