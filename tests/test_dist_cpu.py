@@ -60,3 +60,58 @@ def test_sharded_loss_plumbing_gloo_world2(n, E):
         assert p.exitcode == 0
     res = dict(q.get(timeout=5) for _ in range(world))
     assert res == {0: True, 1: True}
+
+
+def _worker_mmr(rank, world, port, n, E, q):
+    """MaxMarginRankingLoss's rank routing (packed all-gather; local-row gradient by default, reduce-scatter with
+    gather_with_grad) under gloo.  The two kernel calls are replaced by the oracle's arithmetic (CPU has no kernels); the GPU
+    box runs the same check through the kernels over NCCL (tests/test_dist_gpu.py)."""
+    sys.path.insert(0, ROOT)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from avion_b200 import ops
+        from avion_b200.losses import MaxMarginRankingLoss
+        from oracle import ranking_oracle as R
+
+        def mmr_fwd(text, image, margin, fix_norm):                 # workspace = the features themselves
+            return R.max_margin_loss(image, text, margin, fix_norm).detach(), torch.stack([text, image])
+
+        def mmr_bwd(ws, gloss, n_all, E_, margin, fix_norm):
+            with torch.enable_grad():
+                _, di, dt = R.loss_and_grads(ws[1], ws[0], margin, fix_norm)
+            return dt * gloss, di * gloss
+
+        ops.mmr_fwd, ops.mmr_bwd = mmr_fwd, mmr_bwd
+        torch.manual_seed(0)
+        N = world * n
+        g_img = torch.randn(N, E)
+        g_txt = 0.25 * g_img + torch.randn(N, E)
+        off = rank * n
+        full, fdi, fdt = R.loss_and_grads(g_img, g_txt, 0.2, True)
+        ok = True
+        for gwg, factor in ((False, 1.0), (True, float(world))):
+            img = g_img[off:off + n].clone().requires_grad_(True)
+            txt = g_txt[off:off + n].clone().requires_grad_(True)
+            loss = MaxMarginRankingLoss(gather_with_grad=gwg, rank=rank, world_size=world)(img, txt)["loss"]
+            loss.backward()
+            ok = ok and torch.allclose(loss, full, rtol=1e-6) \
+                and torch.allclose(img.grad, factor * fdi[off:off + n], rtol=1e-5, atol=1e-8) \
+                and torch.allclose(txt.grad, factor * fdt[off:off + n], rtol=1e-5, atol=1e-8)
+        q.put((rank, bool(ok)))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_max_margin_rank_routing_gloo_world2():
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29850 + (os.getpid() % 100)
+    procs = [ctx.Process(target=_worker_mmr, args=(r, world, port, 5, 16, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    assert dict(q.get(timeout=5) for _ in range(world)) == {0: True, 1: True}
