@@ -20,8 +20,15 @@ import torch
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
-# stdout carries exactly ONE JSON line: NCCL's version / debug banner (printed to stdout by default) goes to stderr
-os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+# stdout carries exactly ONE JSON line.  NCCL prints its version banner to file descriptor 1 whatever NCCL_DEBUG_FILE says, so
+# fd 1 is pointed at stderr for the whole process and the JSON line goes out through a private duplicate of the real stdout.
+_REAL_STDOUT = os.fdopen(os.dup(1), "w")
+os.dup2(2, 1)
+
+
+def emit(line):
+    _REAL_STDOUT.write(json.dumps(line) + "\n")
+    _REAL_STDOUT.flush()
 
 # algorithmic FLOPs per clip-text pair, forward; train step = 3x (no recompute counted)
 FWD_GFLOP_PER_PAIR = {"vitb16_16f": 905.3, "vitb16_4f": 162.95, "vitl14_16f": 4142.8,
@@ -174,13 +181,13 @@ def run_reference(args):
         n = max(pairs, 48)
         v, ms = cpu_reference_videomae_clips_per_s(n, steps, warmup, threads)
         sample = f"{n} clips/step, fp32, targets+fwd+MSE+bwd+AdamW, {steps} timed steps after {warmup} warm-up"
-        print(json.dumps({"impl": "reference", "metric": "clips/sec VideoMAE ViT-B/16 16f pretrain step", "value": v, "unit": "clips/s",
+        emit({"impl": "reference", "metric": "clips/sec VideoMAE ViT-B/16 16f pretrain step", "value": v, "unit": "clips/s",
                           "n_gpus": args.gpus, "steps": steps, "warmup": warmup, "ms_per_step": ms, "higher_is_better": True,
                           "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                           "config": {"workload": "VideoMAE ViT-B/16 16f 224^2 pretrain step, 90% tube masking (oracle port on host CPU)",
                                      "clips_per_step": n},
                           "cpu_baseline": {"value": v, "unit": "clips/s", "cores": threads, "kind": "port", "sample": sample},
-                          "e2e": {"value": v, "unit": "clips/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}), flush=True)
+                          "e2e": {"value": v, "unit": "clips/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}})
         return
     # bound the whole run to a few minutes: at most 2 timed + 1 warm-up CPU steps of `pairs` pairs (each ~10-40 s)
     steps, warmup = min(args.steps, 2), min(args.warmup, 1)
@@ -192,7 +199,7 @@ def run_reference(args):
             "config": {"workload": f"AVION CLIP ViT-B/16 {args.frames}f 224^2 train step (oracle port on host CPU)", "pairs_per_step": pairs},
             "cpu_baseline": {"value": v, "unit": "clips/s", "cores": threads, "kind": "port", "sample": sample},
             "e2e": {"value": v, "unit": "clips/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # =====================================================================================================================
@@ -376,7 +383,7 @@ def run_ours(args):
             "clocks": clocks, "roofline": roofline, "kernels": fam[:10],
             "step_tensor": {"algorithmic_tflops": step_tf, "peak": pk["tf_sust"], "frac": step_tf / pk["tf_sust"] if step_tf else None},
             "cpu_baseline": cpu_baseline}
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -552,7 +559,7 @@ def run_videomae(args, world, rank, local_rank, dev):
             "clocks": clocks, "roofline": roofline, "kernels": fam[:14],
             "step_tensor": {"algorithmic_tflops": step_tf, "peak": pk["tf_sust"], "frac": step_tf / pk["tf_sust"]},
             "cpu_baseline": cpu_baseline}
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 
