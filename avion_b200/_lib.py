@@ -30,6 +30,7 @@ SIGNATURES = {
     "avn_device_check": [],
     "avn_sample_rrc_boxes": [_u64, _i, _i, _i, _d, _d, _d, _d, _d, _vp],
     "avn_clip_transform_u8_bf16": [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp, C.POINTER(_f), C.POINTER(_f), _vp],
+    "avn_clip_resize_transform_u8_bf16": [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp, C.POINTER(_f), C.POINTER(_f), _vp],
     "avn_layernorm_fwd": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i, _f, _vp],
     "avn_layernorm_bwd": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i, _vp],
     "avn_gemm_bf16": [C.POINTER(GemmDesc), _vp],
@@ -45,8 +46,8 @@ SIGNATURES = {
     "avn_token_embed_bwd": [_vp, _vp, _vp, _vp, _i, _i, _i, _vp],
     "avn_head_fwd": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _f, _vp],
     "avn_head_bwd": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp],
-    "avn_infonce_fwd": [_vp, _vp, _vp, _vp, _f, _i, _i, _i, _i, _vp, _vp, _vp],
-    "avn_infonce_bwd": [_vp, _vp, _vp, _vp, _f, _i, _i, _i, _i, _vp, _f, _vp, _vp, _vp, _vp],
+    "avn_infonce_fwd": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp],
+    "avn_infonce_bwd": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp, _f, _i, _vp, _vp, _vp, _vp],
     "avn_adamw_chunk_elems": [],
     "avn_adamw_step": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _f, _f, _f, _f, _i, _vp],
     "avn_clamp_scalar_f32": [_vp, _f, _f, _vp],

@@ -33,9 +33,10 @@ constexpr long long G1_LAG_CYCLES = AVN_FWD_LAG;      // head start of softmax g
 
 // Optional phase trace (debug aid, off unless avn_debug_set_attn_fwd_trace is given a buffer): CTA (0,0,0) records clock64 at
 // phase boundaries as trace[(role * 32 + iteration) * 16 + slot]; role 0 / 1 = first warp of softmax group 0 / 1.
-// Compiled in only with -DAVN_TRACE (the extra predicated stores cost ~4 % in the softmax loop).
-__device__ long long* g_trace_fwd = nullptr;
+// Compiled in only with -DAVN_TRACE (the extra predicated stores cost ~4 % in the softmax loop); the default build has no
+// device global and no debug entry point.
 #ifdef AVN_TRACE
+__device__ long long* g_trace_fwd = nullptr;
 #define TRF(role, it, slot)                                                                            \
     do {                                                                                               \
         if (trace && lane == 0 && (it) < 32) trace[((role) * 32 + (it)) * 16 + (slot)] = clock64();   \
@@ -77,13 +78,16 @@ __device__ __forceinline__ float row_max(const uint32_t* sv, int limit) {
 #ifndef AVN_FWD_POLY_DEN
 #define AVN_FWD_POLY_DEN 3
 #endif
+// POLY = false: every exponential on the MUFU.  Used for short sequences (one or two K/V tiles: the tiny parity fixtures, the
+// text tower), where the kernel is latency-bound and the FMA-pipe exponentials buy nothing.
+template <bool POLY>
 __device__ __forceinline__ float2 exp2_pair(float2 x, int pair_index) {
-    if ((pair_index % AVN_FWD_POLY_DEN) < AVN_FWD_POLY_NUM) return exp2_poly2(x);
+    if (POLY && (pair_index % AVN_FWD_POLY_DEN) < AVN_FWD_POLY_NUM) return exp2_poly2(x);
     return make_float2(ex2(x.x), ex2(x.y));
 }
 
 // p = exp2(s * scale_log2 - m_ref) for one row of 128 scores -> packed bf16 pairs; returns the row sum
-template <bool MASK>
+template <bool MASK, bool POLY>
 __device__ __forceinline__ float row_exp(const uint32_t* sv, uint32_t* pk, float scale_log2, float m_ref, int limit) {
     const float2 sc2 = make_float2(scale_log2, scale_log2), nm2 = make_float2(-m_ref, -m_ref);
     float2 r0 = make_float2(0.f, 0.f), r1 = make_float2(0.f, 0.f);
@@ -91,7 +95,7 @@ __device__ __forceinline__ float row_exp(const uint32_t* sv, uint32_t* pk, float
     for (int i = 0; i < TILE / 2; i += 2) {
         const float2 x0 = __ffma2_rn(make_float2(__uint_as_float(sv[2 * i]), __uint_as_float(sv[2 * i + 1])), sc2, nm2);
         const float2 x1 = __ffma2_rn(make_float2(__uint_as_float(sv[2 * i + 2]), __uint_as_float(sv[2 * i + 3])), sc2, nm2);
-        float2 e0 = exp2_pair(x0, i), e1 = exp2_pair(x1, i + 1);
+        float2 e0 = exp2_pair<POLY>(x0, i), e1 = exp2_pair<POLY>(x1, i + 1);
         if (MASK) {
             if (2 * i >= limit) e0.x = 0.f;
             if (2 * i + 1 >= limit) e0.y = 0.f;
@@ -104,6 +108,7 @@ __device__ __forceinline__ float row_exp(const uint32_t* sv, uint32_t* pk, float
     return (r0.x + r0.y) + (r1.x + r1.y);
 }
 
+template <bool POLY>
 __global__ void __launch_bounds__(NTHREADS, 1)
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmO, float* __restrict__ lse,
                 int S, int H, float scale_log2, int causal) {
@@ -262,8 +267,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
                 m_ref = m_new;
                 uint32_t pk[TILE / 2];
                 float rs;
-                if (need_mask) rs = row_exp<true>(sv, pk, scale_log2, m_ref, limit);
-                else rs = row_exp<false>(sv, pk, scale_log2, m_ref, limit);
+                if (need_mask) rs = row_exp<true, POLY>(sv, pk, scale_log2, m_ref, limit);
+                else rs = row_exp<false, POLY>(sv, pk, scale_log2, m_ref, limit);
                 l = fmaf(l, alpha, rs);
                 TRF(w, j, 4);
                 // P V of tile j-1 must have completed: the MMA has finished reading this group's P buffer and O is stable
@@ -338,10 +343,12 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
 }
 }  // namespace
 
+#ifdef AVN_TRACE
 extern "C" int avn_debug_set_attn_fwd_trace(long long* buf) {
     AVN_CHECK_CUDA(cudaMemcpyToSymbol(g_trace_fwd, &buf, sizeof(buf)));
     return AVN_OK;
 }
+#endif
 
 extern "C" int avn_attn_fwd(const void* qkv, void* out, float* lse, int B, int S, int H, float scale, int causal, avn_stream_t stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
@@ -363,9 +370,11 @@ extern "C" int avn_attn_fwd(const void* qkv, void* out, float* lse, int B, int S
         if ((rc = avn_make_tmap(&tmO, out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, 3, dims, str, box, true))) return rc;
     }
     const int q_tiles = (S + TILE - 1) / TILE;
-    AVN_CHECK_CUDA(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_TOTAL));
+    // long sequences: a third of the exponentials on the FMA pipe (MUFU-bound kernel); S <= 256: all on the MUFU
+    auto kern = S > 2 * TILE ? attn_fwd_kernel<true> : attn_fwd_kernel<false>;
+    AVN_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_TOTAL));
     dim3 grid((q_tiles + 1) / 2, H, B);
-    attn_fwd_kernel<<<grid, NTHREADS, SMEM_TOTAL, stream>>>(tmQKV, tmO, lse, S, H, scale * 1.4426950408889634f, causal);
+    kern<<<grid, NTHREADS, SMEM_TOTAL, stream>>>(tmQKV, tmO, lse, S, H, scale * 1.4426950408889634f, causal);
     AVN_CHECK_CUDA(cudaGetLastError());
     return AVN_OK;
 }

@@ -14,10 +14,11 @@ constexpr int ROWS = 8;
 template <bool BWD>
 __global__ void __launch_bounds__(256)
 infonce_rows_kernel(const float* __restrict__ img, const float* __restrict__ txt, const float* __restrict__ all_img,
-                    const float* __restrict__ all_txt, float scale, int n, int N, int E, int row_offset,
+                    const float* __restrict__ all_txt, const float* __restrict__ scale_ptr, int n, int N, int E, int row_offset,
                     float* __restrict__ lse, float* __restrict__ out, float gcoef, float* __restrict__ dlogits,
                     float* __restrict__ dscale) {
     extern __shared__ float sm[];
+    const float scale = __ldg(scale_ptr);     // logit_scale.exp() stays on the device: no host read of a parameter per step
     float* rows = sm;                         // [ROWS][E]
     float* red = sm + ROWS * E;               // [8 warps][ROWS][4]
     const int dir = blockIdx.y;
@@ -144,9 +145,9 @@ infonce_drows_kernel(const float* __restrict__ all_img, const float* __restrict_
 }
 }  // namespace
 
-extern "C" int avn_infonce_fwd(const float* img, const float* txt, const float* all_img, const float* all_txt, float scale,
+extern "C" int avn_infonce_fwd(const float* img, const float* txt, const float* all_img, const float* all_txt, const float* scale,
                                int n, int N, int E, int row_offset, float* lse, float* out, avn_stream_t stream_) {
-    AVN_REQUIRE(img && txt && all_img && all_txt && lse && out, "infonce_fwd: null pointer");
+    AVN_REQUIRE(img && txt && all_img && all_txt && scale && lse && out, "infonce_fwd: null pointer");
     AVN_REQUIRE(n > 0 && N >= n && E > 0 && E % 4 == 0 && row_offset >= 0 && row_offset + n <= N, "infonce_fwd: bad sizes n=%d N=%d E=%d off=%d", n, N, E, row_offset);
     const size_t smem = (size_t)(ROWS * E + 8 * ROWS * 4) * sizeof(float);
     auto kern = infonce_rows_kernel<false>;
@@ -157,11 +158,11 @@ extern "C" int avn_infonce_fwd(const float* img, const float* txt, const float* 
     return AVN_OK;
 }
 
-extern "C" int avn_infonce_bwd(const float* img, const float* txt, const float* all_img, const float* all_txt, float scale,
-                               int n, int N, int E, int row_offset, const float* lse, float gscale, float* dlogits, float* d_all,
-                               float* dscale, avn_stream_t stream_) {
+extern "C" int avn_infonce_bwd(const float* img, const float* txt, const float* all_img, const float* all_txt, const float* scale,
+                               int n, int N, int E, int row_offset, const float* lse, float gscale, int col_side, float* dlogits,
+                               float* d_all, float* dscale, avn_stream_t stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
-    AVN_REQUIRE(img && txt && all_img && all_txt && lse && dlogits && d_all && dscale, "infonce_bwd: null pointer");
+    AVN_REQUIRE(img && txt && all_img && all_txt && scale && lse && dlogits && d_all && dscale, "infonce_bwd: null pointer");
     AVN_REQUIRE(n > 0 && N >= n && E > 0 && E % 4 == 0 && row_offset >= 0 && row_offset + n <= N, "infonce_bwd: bad sizes");
     const size_t smem = (size_t)(ROWS * E + 8 * ROWS * 4) * sizeof(float);
     auto kern = infonce_rows_kernel<true>;
@@ -170,8 +171,10 @@ extern "C" int avn_infonce_bwd(const float* img, const float* txt, const float* 
                                                               const_cast<float*>(lse), nullptr, gscale * 0.5f / n, dlogits, dscale);
     AVN_CHECK_CUDA(cudaGetLastError());
     const long long nc = (long long)N * E, nr = (long long)n * E;
-    infonce_dcols_kernel<<<dim3((unsigned)((nc + 255) / 256), 2), 256, 0, stream>>>(img, txt, dlogits, d_all, n, N, E);
-    AVN_CHECK_CUDA(cudaGetLastError());
+    if (col_side) {      // gathered operands that carry no gradient (losses.py:61-72 with local_loss) get no column-side term
+        infonce_dcols_kernel<<<dim3((unsigned)((nc + 255) / 256), 2), 256, 0, stream>>>(img, txt, dlogits, d_all, n, N, E);
+        AVN_CHECK_CUDA(cudaGetLastError());
+    }
     infonce_drows_kernel<<<dim3((unsigned)((nr + 255) / 256), 2), 256, 0, stream>>>(all_img, all_txt, dlogits, d_all, n, N, E, row_offset);
     AVN_CHECK_CUDA(cudaGetLastError());
     return AVN_OK;

@@ -14,14 +14,18 @@ STD_TIMM = (0.229 * 255, 0.224 * 255, 0.225 * 255)
 class GPUClipTransform(nn.Module):
     """uint8 decord frames [B,T,Hs,Ws,3] -> bf16 patches [B, T*(crop/patch)^2, 3*patch^2] in one kernel.
 
-    boxes (optional): int32 [B,3] = (x, y, hflip) per clip; use `sample_boxes` for decord-style random crops of a fixed
-    crop x crop window (the resize step of decord's filter graph lives in ffmpeg and is out of scope)."""
+    boxes (optional, int32 on the clips' device), one row per clip:
+      [B,3] = (x, y, hflip)       crop a crop x crop window at (x, y) - no resize;
+      [B,5] = (x, y, w, h, hflip) decord's random-RESIZED crop: the w x h box at (x, y) is resized to crop x crop
+                                  (antialiased bilinear, rounded to uint8 like decoded frames) - rows of `sample_boxes`."""
 
     def __init__(self, crop=224, patch=16, mean=MEAN_OPENAI, std=STD_OPENAI):
         super().__init__()
         self.crop, self.patch, self.mean, self.std = crop, patch, tuple(mean), tuple(std)
 
     def forward(self, frames_u8, boxes=None):
+        if boxes is not None and boxes.shape[-1] == 5:
+            return ops.clip_resize_transform(frames_u8, boxes, self.crop, self.patch, self.mean, self.std)
         return ops.clip_transform(frames_u8, self.crop, self.patch, self.mean, self.std, boxes=boxes)
 
     @staticmethod

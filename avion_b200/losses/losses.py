@@ -19,7 +19,7 @@ class _InfoNCEFn(torch.autograd.Function):
             all_img, all_txt = both[0], both[1]
         else:
             all_img, all_txt = img32, txt32
-        s = float(scale.detach())
+        s = scale.detach().float().reshape(1).contiguous()      # stays on the device: no host read of the parameter per step
         off = rank * n
         lse, out = ops.infonce_fwd(img32, txt32, all_img, all_txt, s, off)
         stats = torch.stack([out[0] / n, 100.0 * out[1] / n])                  # rank-local mean loss, top-1 accuracy
@@ -27,23 +27,36 @@ class _InfoNCEFn(torch.autograd.Function):
             # the reference's default mode evaluates the full NxN problem on every rank (:119-123); its scalar is the
             # mean over all N rows = the mean of the rank-local means
             stats = _dist.mean_over_ranks(stats, world, group)
-        ctx.save_for_backward(img32, txt32, all_img, all_txt, lse)
-        ctx.cfg = (s, off, rank, world, local_loss, gather_with_grad, group, img.dtype, txt.dtype)
+        ctx.save_for_backward(img32, txt32, all_img, all_txt, lse, s)
+        ctx.cfg = (off, rank, world, local_loss, gather_with_grad, group, img.dtype, txt.dtype)
         loss, acc = stats[0].clone(), stats[1].clone()
         ctx.mark_non_differentiable(acc)
         return loss, acc
 
     @staticmethod
     def backward(ctx, gloss, _gacc):
-        img32, txt32, all_img, all_txt, lse = ctx.saved_tensors
-        s, off, rank, world, local_loss, gather_with_grad, group, dt_i, dt_t = ctx.cfg
+        img32, txt32, all_img, all_txt, lse, s = ctx.saved_tensors
+        off, rank, world, local_loss, gather_with_grad, group, dt_i, dt_t = ctx.cfg
         n, E = img32.shape
-        d_all, dscale = ops.infonce_bwd(img32, txt32, all_img, all_txt, s, off, lse, 1.0)
-        if world > 1 and (gather_with_grad or not local_loss):
+        # The four modes of gather_features (avion/losses/losses.py:53-75) with the loss of :116-133:
+        #   gather_with_grad             : every rank's loss reaches every rank's features (all_gather backward = sum over ranks)
+        #   neither                      : full-matrix loss, remote features constant, own slice re-inserted (:68-72)
+        #                                  = 1/W of the sum of the rank-local losses' gradients
+        #   local_loss only              : the gathered copies carry NO gradient and the own slice is NOT re-inserted, so only
+        #                                  the row side (the direct use of image_features / text_features, :117-118) flows
+        rows_only = world > 1 and local_loss and not gather_with_grad
+        d_all, dscale = ops.infonce_bwd(img32, txt32, all_img, all_txt, s, off, lse, 1.0, col_side=not rows_only)
+        if world > 1 and not rows_only:
             # d_all holds this rank's contribution to every rank's features: sum them where they belong
-            local = _dist.scatter_sum(d_all, world, group)
+            if local_loss:
+                local = _dist.scatter_sum(d_all, world, group)
+            else:
+                # full-matrix loss: every rank's reference backward holds d(full loss)/d scale = the mean of the rank-local
+                # ones; it rides in the same reduce-scatter
+                local, dsum = _dist.scatter_sum(d_all, world, group, extra=dscale)
+                dscale = dsum / world
             if not gather_with_grad:
-                local = local / world       # full-matrix loss with constant remote features (:62-72) == 1/W of the sum
+                local = local / world
         else:
             local = d_all[:, off:off + n]
         g = gloss.float()

@@ -1,6 +1,8 @@
 """Tensor-level wrappers of the C-ABI kernels (one function per entry point of include/avion_b200.h).
 
-PyTorch is used only for device memory and streams.  Every function launches on torch's current CUDA stream.
+Every launch goes through the registered torch custom operator of that entry point (`torch.ops.avion_b200.<name>`,
+avion_b200/torch_ops.py), whose CUDA implementation is the ctypes call.  PyTorch is used only for device memory, streams and
+operator dispatch.  Every function launches on torch's current CUDA stream.
 """
 import ctypes as C
 
@@ -9,6 +11,7 @@ import torch
 from . import _lib
 from ._lib import (EPI_BIAS, EPI_BIAS_GELU, EPI_BIAS_GELU_DUAL, EPI_BIAS_RESIDUAL, EPI_DGELU, EPI_F32_ADD, EPI_NONE,
                    GEMM_NN, GEMM_NT, GEMM_TN, GemmDesc)
+from .torch_ops import K
 
 bf16, f32 = torch.bfloat16, torch.float32
 _checked_devices = set()
@@ -39,15 +42,17 @@ class _timed:
             TIMED.setdefault(self.name, []).append((self.s, self.e, self.work))
 
 
+def _cuda(t):
+    """No CPU fallback: refuse anything that is not a CUDA tensor before the dispatcher does."""
+    if t.device.type != "cuda":
+        raise RuntimeError("avion_b200 kernels run on CUDA (sm_100a) tensors only; got a %s tensor" % t.device.type)
+    return t
+
+
 def _stream(t):
-    dev = t.device
-    if dev.type != "cuda":
-        raise RuntimeError("avion_b200 kernels run on CUDA (sm_100a) tensors only; got a %s tensor" % dev.type)
-    if dev.index not in _checked_devices:
-        with torch.cuda.device(dev):
-            _lib.call("avn_device_check")
-        _checked_devices.add(dev.index)
-    return C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+    """Raw stream handle for the few direct ctypes callers outside this module (graph capture helpers)."""
+    from .torch_ops import _stream_of
+    return _stream_of(_cuda(t))
 
 
 def _p(t):
@@ -83,11 +88,23 @@ def clip_transform(frames_u8, crop, patch, mean, std, boxes=None, out=None):
     if boxes is not None:
         _chk(boxes, torch.int32, "boxes")
         assert boxes.shape == (B, 3) and boxes.device == frames_u8.device
-    m = (C.c_float * 3)(*[float(v) for v in mean])
-    s = (C.c_float * 3)(*[float(v) for v in std])
-    with _timed("clip_transform", frames_u8, 3.0 * frames_u8.numel()):
-        _lib.call("avn_clip_transform_u8_bf16", _p(frames_u8), _p(out), B, T, Hs, Ws, crop, patch, _p(boxes), m, s,
-                  _stream(frames_u8))
+    with _timed("clip_transform", _cuda(frames_u8), 3.0 * frames_u8.numel()):
+        K.clip_transform_u8_bf16(frames_u8, out, B, T, Hs, Ws, crop, patch, boxes, [float(v) for v in mean], [float(v) for v in std])
+    return out
+
+
+def clip_resize_transform(frames_u8, boxes, crop, patch, mean, std, out=None):
+    """uint8 [B,T,Hs,Ws,3] + boxes int32 [B,5] = (x, y, w, h, hflip) (the rows avn_sample_rrc_boxes writes) -> bf16 patches
+    [B, T*(crop/patch)^2, F] of each clip's box resized to crop x crop (antialiased bilinear, rounded to the uint8 grid)."""
+    _chk(frames_u8, torch.uint8, "frames"); _chk(boxes, torch.int32, "boxes")
+    B, T, Hs, Ws, ch = frames_u8.shape
+    assert ch == 3 and boxes.shape == (B, 5) and boxes.device == frames_u8.device
+    g = crop // patch
+    if out is None:
+        out = torch.empty(B, T * g * g, patch_features(patch), dtype=bf16, device=frames_u8.device)
+    with _timed("clip_resize_transform", _cuda(frames_u8), float(frames_u8.numel()) + 2.0 * out.numel()):
+        K.clip_resize_transform_u8_bf16(frames_u8, out, B, T, Hs, Ws, crop, patch, boxes, [float(v) for v in mean],
+                                        [float(v) for v in std])
     return out
 
 
@@ -100,8 +117,8 @@ def layernorm_fwd(x, gamma, beta, eps, out=None, save_stats=True):
     if save_stats:
         mean = torch.empty(rows, dtype=f32, device=x.device)
         rstd = torch.empty(rows, dtype=f32, device=x.device)
-    with _timed("layernorm_fwd", x, 4.0 * rows * D):
-        _lib.call("avn_layernorm_fwd", _p(x), _p(gamma), _p(beta), _p(y), _p(mean), _p(rstd), rows, D, float(eps), _stream(x))
+    with _timed("layernorm_fwd", _cuda(x), 4.0 * rows * D):
+        K.layernorm_fwd(x, gamma, beta, y, mean, rstd, rows, D, float(eps))
     return y, mean, rstd
 
 
@@ -111,22 +128,18 @@ def layernorm_bwd(dy, x, gamma, mean, rstd, dgamma, dbeta, dres=None, dcolsum=No
     rows = x.numel() // D
     dx = out if out is not None else torch.empty_like(x)
     with _timed("layernorm_bwd", x, (8.0 if dres is not None else 6.0) * rows * D):
-        _lib.call("avn_layernorm_bwd", _p(dy), _p(x), _p(gamma), _p(mean), _p(rstd), _p(dres), _p(dx), _p(dgamma), _p(dbeta),
-                  _p(dcolsum), rows, D, _stream(x))
+        K.layernorm_bwd(dy, _cuda(x), gamma, mean, rstd, dres, dx, dgamma, dbeta, dcolsum, rows, D)
     return dx
 
 
-def gemm(mode, epi, M, N, K, A, lda, B, ldb, Cm, ldc, batch=1, a_bs=0, b_bs=0, c_bs=0, C2=None, bias=None, R=None, ldr=0,
+def gemm(mode, epi, M, N, Kd, A, lda, B, ldb, Cm, ldc, batch=1, a_bs=0, b_bs=0, c_bs=0, C2=None, bias=None, R=None, ldr=0,
          r_bs=0, splits=1):
     """Raw descriptor-level GEMM (see include/avion_b200.h); A/B/Cm/C2/R are tensors whose data_ptr is the origin."""
-    d = GemmDesc(mode, epi, M, N, K, batch, A.data_ptr(), lda, a_bs, B.data_ptr(), ldb, b_bs, Cm.data_ptr(), ldc, c_bs,
-                 C2.data_ptr() if C2 is not None else None, bias.data_ptr() if bias is not None else None,
-                 R.data_ptr() if R is not None else None, ldr, r_bs, splits)
     name = "gemm_%s" % ("nt", "nn", "tn")[mode]
     if TIMED_BY_EPILOGUE:
         name += "_" + _EPI_NAMES[epi]
-    with _timed(name, A, 2.0 * M * N * K * batch):
-        _lib.call("avn_gemm_bf16", C.byref(d), _stream(A))
+    with _timed(name, _cuda(A), 2.0 * M * N * Kd * batch):
+        K.gemm_bf16(mode, epi, M, N, Kd, batch, A, lda, a_bs, B, ldb, b_bs, Cm, ldc, c_bs, C2, bias, R, ldr, r_bs, splits)
 
 
 def linear_fwd(x, w, bias=None, epi=EPI_NONE, residual=None, out=None, out2=None):
@@ -170,7 +183,7 @@ def attn_fwd(qkv, heads, scale, causal=False, out=None):
     o = out if out is not None else torch.empty(B, S, heads * 64, dtype=bf16, device=qkv.device)
     lse = torch.empty(B, heads, S, dtype=f32, device=qkv.device)
     with _timed("attn_fwd", qkv, (2.0 if causal else 4.0) * B * heads * S * S * 64):
-        _lib.call("avn_attn_fwd", _p(qkv), _p(o), _p(lse), B, S, heads, float(scale), int(causal), _stream(qkv))
+        K.attn_fwd(_cuda(qkv), o, lse, B, S, heads, float(scale), bool(causal))
     return o, lse
 
 
@@ -183,15 +196,14 @@ def attn_bwd(qkv, o, do, lse, heads, scale, causal=False, dqkv=None, dq_acc=None
     if dq_acc is None:
         dq_acc = torch.empty(B, S, heads * 64, dtype=f32, device=qkv.device)
     with _timed("attn_bwd", qkv, (5.0 if causal else 10.0) * B * heads * S * S * 64):
-        _lib.call("avn_attn_bwd", _p(qkv), _p(o), _p(do), _p(lse), _p(dqkv), _p(delta), _p(dq_acc), B, S, heads, float(scale),
-                  int(causal), _stream(qkv))
+        K.attn_bwd(_cuda(qkv), o, do, lse, dqkv, delta, dq_acc, B, S, heads, float(scale), bool(causal))
     return dqkv
 
 
 def cast_bf16(src, out=None):
     _chk(src, f32, "src")
     dst = out if out is not None else torch.empty(src.shape, dtype=bf16, device=src.device)
-    _lib.call("avn_cast_f32_bf16", _p(src), _p(dst), src.numel(), _stream(src))
+    K.cast_f32_bf16(_cuda(src), dst, src.numel())
     return dst
 
 
@@ -199,7 +211,7 @@ def transpose_cast_bf16(src):
     _chk(src, f32, "src")
     r, c = src.shape
     dst = torch.empty(c, r, dtype=bf16, device=src.device)
-    _lib.call("avn_transpose_cast_f32_bf16", _p(src), _p(dst), r, c, _stream(src))
+    K.transpose_cast_f32_bf16(_cuda(src), dst, r, c)
     return dst
 
 
@@ -208,25 +220,25 @@ def colsum(x, out):
     _chk(x, bf16, "x"); _chk(out, f32, "out")
     N = x.shape[-1]
     with _timed("colsum", x, 2.0 * x.numel()):
-        _lib.call("avn_colsum_bf16", _p(x), N, _p(out), x.numel() // N, N, _stream(x))
+        K.colsum_bf16(_cuda(x), N, out, x.numel() // N, N)
     return out
 
 
 def pos_table_fwd(cls, pos, temporal, T, G):
     D = cls.numel()
     table = torch.empty(T * G + 1, D, dtype=bf16, device=cls.device)
-    _lib.call("avn_pos_table_fwd", _p(cls), _p(pos), _p(temporal), _p(table), T, G, D, _stream(cls))
+    K.pos_table_fwd(_cuda(cls), pos, temporal, table, T, G, D)
     return table
 
 
 def broadcast_row(x, row, B, batch_stride, D):
-    _lib.call("avn_broadcast_row", _p(x), _p(row), B, batch_stride, D, _stream(x))
+    K.broadcast_row(_cuda(x), row, B, batch_stride, D)
 
 
 def pos_table_bwd(dx, dcls, dpos, dtemporal, T, G):
     B, S, D = dx.shape
     ws = torch.empty(S, D, dtype=f32, device=dx.device)
-    _lib.call("avn_pos_table_bwd", _p(dx), _p(ws), _p(dcls), _p(dpos), _p(dtemporal), B, T, G, D, _stream(dx))
+    K.pos_table_bwd(_cuda(dx), ws, dcls, dpos, dtemporal, B, T, G, D)
 
 
 def token_embed_fwd(ids, tok_emb, pos):
@@ -234,13 +246,13 @@ def token_embed_fwd(ids, tok_emb, pos):
     B, L = ids.shape
     D = tok_emb.shape[1]
     x = torch.empty(B, L, D, dtype=bf16, device=ids.device)
-    _lib.call("avn_token_embed_fwd", _p(ids), _p(tok_emb), _p(pos), _p(x), B, L, D, _stream(x))
+    K.token_embed_fwd(_cuda(ids), tok_emb, pos, x, B, L, D)
     return x
 
 
 def token_embed_bwd(ids, dx, dtok, dpos):
     B, L, D = dx.shape
-    _lib.call("avn_token_embed_bwd", _p(ids), _p(dx), _p(dtok), _p(dpos), B, L, D, _stream(dx))
+    K.token_embed_bwd(ids, _cuda(dx), dtok, dpos, B, L, D)
 
 
 def head_fwd(x2d, row_idx, gamma, beta, proj, eps):
@@ -253,8 +265,7 @@ def head_fwd(x2d, row_idx, gamma, beta, proj, eps):
     u = torch.empty(n, E, dtype=f32, device=dev)
     mean = torch.empty(n, dtype=f32, device=dev)
     rstd = torch.empty(n, dtype=f32, device=dev)
-    _lib.call("avn_head_fwd", _p(x2d), _p(row_idx), _p(gamma), _p(beta), _p(proj), _p(emb), _p(u), _p(mean), _p(rstd), n, D, E,
-              float(eps), _stream(x2d))
+    K.head_fwd(_cuda(x2d), row_idx, gamma, beta, proj, emb, u, mean, rstd, n, D, E, float(eps))
     return emb, (u, mean, rstd)
 
 
@@ -264,33 +275,37 @@ def head_bwd(demb, x2d, row_idx, gamma, beta, proj, saved, dx2d, dgamma, dbeta, 
     D, E = proj.shape
     ws = torch.empty(n, D + E, dtype=f32, device=x2d.device)
     _chk(demb, f32, "demb")
-    _lib.call("avn_head_bwd", _p(demb), _p(x2d), _p(row_idx), _p(gamma), _p(beta), _p(proj), _p(u), _p(mean), _p(rstd), _p(dx2d),
-              _p(dgamma), _p(dbeta), _p(dproj), _p(ws), n, D, E, int(normalized), _stream(x2d))
+    K.head_bwd(demb, _cuda(x2d), row_idx, gamma, beta, proj, u, mean, rstd, dx2d, dgamma, dbeta, dproj, ws, n, D, E, bool(normalized))
 
 
 def infonce_fwd(img, txt, all_img, all_txt, scale, row_offset):
-    """-> (lse [2,n], out [2] = (sum of per-row (CE_i+CE_t)/2, number of correct image->text argmaxes))."""
+    """scale: fp32 CUDA tensor with one element (logit_scale.exp(); read on the device, no host sync)
+    -> (lse [2,n], out [2] = (sum of per-row (CE_i+CE_t)/2, number of correct image->text argmaxes))."""
+    _chk(scale, f32, "scale")
+    assert scale.numel() == 1
     for t, nm in ((img, "img"), (txt, "txt"), (all_img, "all_img"), (all_txt, "all_txt")):
         _chk(t, f32, nm)
     n, E = img.shape
     N = all_img.shape[0]
     lse = torch.empty(2, n, dtype=f32, device=img.device)
     out = torch.zeros(2, dtype=f32, device=img.device)
-    _lib.call("avn_infonce_fwd", _p(img), _p(txt), _p(all_img), _p(all_txt), float(scale), n, N, E, row_offset, _p(lse), _p(out),
-              _stream(img))
+    with _timed("infonce", _cuda(img), 8.0 * (n + N) * E):
+        K.infonce_fwd(img, txt, all_img, all_txt, scale, n, N, E, row_offset, lse, out)
     return lse, out
 
 
-def infonce_bwd(img, txt, all_img, all_txt, scale, row_offset, lse, gscale):
-    """-> (d_all fp32 [2,N,E] (image block, text block), dscale fp32 [1])."""
+def infonce_bwd(img, txt, all_img, all_txt, scale, row_offset, lse, gscale, col_side=True):
+    """-> (d_all fp32 [2,N,E] (image block, text block), dscale fp32 [1]).  col_side=False: row-side gradient only (the
+    gathered operands carry no gradient: the reference's local_loss=True, gather_with_grad=False mode)."""
     n, E = img.shape
     N = all_img.shape[0]
     dev = img.device
     dlogits = torch.empty(2, n, N, dtype=f32, device=dev)
     d_all = torch.zeros(2, N, E, dtype=f32, device=dev)
     dscale = torch.zeros(1, dtype=f32, device=dev)
-    _lib.call("avn_infonce_bwd", _p(img), _p(txt), _p(all_img), _p(all_txt), float(scale), n, N, E, row_offset, _p(lse),
-              float(gscale), _p(dlogits), _p(d_all), _p(dscale), _stream(img))
+    with _timed("infonce", _cuda(img), 8.0 * (n + N) * E + 8.0 * n * N + 8.0 * N * E):
+        K.infonce_bwd(img, txt, all_img, all_txt, scale, n, N, E, row_offset, lse, float(gscale), bool(col_side), dlogits, d_all,
+                      dscale)
     return d_all, dscale
 
 
@@ -304,7 +319,7 @@ def tube_mask_slots(mask):
     slot = torch.empty(B, N, dtype=torch.int32, device=mask.device)
     order = torch.empty(B, N, dtype=torch.int32, device=mask.device)
     counts = torch.empty(B, dtype=torch.int32, device=mask.device)
-    _lib.call("avn_tube_mask_slots", _p(mask), _p(slot), _p(order), _p(counts), B, N, _stream(mask))
+    K.tube_mask_slots(_cuda(mask), slot, order, counts, B, N)
     return slot, order, counts
 
 
@@ -320,12 +335,10 @@ def tubelet_transform(frames_u8, slot, n_visible, patch, mean, std, want_patches
     dev = frames_u8.device
     patches = torch.empty(B, n_visible, F, dtype=bf16, device=dev) if want_patches else None
     targets = torch.empty(B, N - n_visible, F, dtype=f32, device=dev) if want_targets else None
-    m = (C.c_float * 3)(*[float(v) for v in mean])
-    s = (C.c_float * 3)(*[float(v) for v in std])
     work = float(frames_u8.numel()) * (1.0 + (2.0 * n_visible + 4.0 * (N - n_visible)) / N)
-    with _timed("tubelet_transform", frames_u8, work):
-        _lib.call("avn_tubelet_transform_u8", _p(frames_u8), _p(slot), _p(patches), _p(targets), B, T, Hs, patch, n_visible, m, s,
-                  _stream(frames_u8))
+    with _timed("tubelet_transform", _cuda(frames_u8), work):
+        K.tubelet_transform_u8(frames_u8, slot, patches, targets, B, T, Hs, patch, n_visible, [float(v) for v in mean],
+                               [float(v) for v in std])
     return patches, targets
 
 
@@ -335,14 +348,14 @@ def gather_rows(table, order, n, add_row=None, add_from=0):
     B, N = order.shape
     D = table.shape[1]
     out = torch.empty(B, n, D, dtype=bf16, device=table.device)
-    _lib.call("avn_gather_rows_f32_bf16", _p(table), _p(order), N, _p(add_row), add_from, _p(out), B, n, D, _stream(table))
+    K.gather_rows_f32_bf16(_cuda(table), order, N, add_row, add_from, out, B, n, D)
     return out
 
 
 def colsum_batched(x, B, batch_stride, rows, cols, out):
     """out[cols] (fp32) += sum over batches and rows of a [rows, cols] bf16 block at x + b*batch_stride."""
     _chk(out, f32, "out")
-    _lib.call("avn_colsum_batched_bf16", _p(x), B, batch_stride, rows, cols, _p(out), _stream(x))
+    K.colsum_batched_bf16(_cuda(x), B, batch_stride, rows, cols, out)
     return out
 
 
@@ -352,7 +365,7 @@ def mse_fwd(pred, target):
     ws = torch.empty(_lib.load().avn_mse_workspace_floats(), dtype=f32, device=pred.device)
     loss = torch.empty((), dtype=f32, device=pred.device)
     with _timed("mse", pred, 6.0 * pred.numel()):
-        _lib.call("avn_mse_fwd", _p(pred), _p(target), pred.numel(), _p(ws), _p(loss), _stream(pred))
+        K.mse_fwd(_cuda(pred), target, pred.numel(), ws, loss)
     return loss
 
 
@@ -360,7 +373,7 @@ def mse_bwd(pred, target, gloss):
     _chk(gloss, f32, "gloss")
     dpred = torch.empty_like(pred)
     with _timed("mse", pred, 8.0 * pred.numel()):
-        _lib.call("avn_mse_bwd", _p(pred), _p(target), _p(gloss), pred.numel(), _p(dpred), _stream(pred))
+        K.mse_bwd(_cuda(pred), target, gloss, pred.numel(), dpred)
     return dpred
 
 
@@ -371,7 +384,7 @@ def mmr_fwd(text, image, margin, fix_norm):
     n, E = text.shape
     ws = torch.empty(_lib.load().avn_mmr_workspace_floats(n, E), dtype=f32, device=text.device)
     loss = torch.empty((), dtype=f32, device=text.device)
-    _lib.call("avn_mmr_fwd", _p(text), _p(image), n, E, float(margin), int(bool(fix_norm)), _p(ws), _p(loss), _stream(text))
+    K.mmr_fwd(_cuda(text), image, n, E, float(margin), bool(fix_norm), ws, loss)
     return loss, ws
 
 
@@ -379,5 +392,5 @@ def mmr_bwd(ws, gloss, n, E, margin, fix_norm):
     _chk(gloss, f32, "gloss")
     dtext = torch.empty(n, E, dtype=f32, device=ws.device)
     dimage = torch.empty(n, E, dtype=f32, device=ws.device)
-    _lib.call("avn_mmr_bwd", _p(ws), _p(gloss), n, E, float(margin), int(bool(fix_norm)), _p(dtext), _p(dimage), _stream(ws))
+    K.mmr_bwd(_cuda(ws), gloss, n, E, float(margin), bool(fix_norm), dtext, dimage)
     return dtext, dimage

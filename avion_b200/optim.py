@@ -8,7 +8,7 @@ weight_decay)` with a weight-decay and a no-weight-decay group); same update, sa
 import torch
 
 from . import _lib
-from .ops import _p, _stream
+from .torch_ops import K
 
 
 class FusedAdamW(torch.optim.Optimizer):
@@ -68,12 +68,11 @@ class FusedAdamW(torch.optim.Optimizer):
         for k, v in launches.items():
             t = self._tables[1][k[:4] + k[5:]]
             lr, b1, b2, eps, step, dev = k
-            _lib.call("avn_adamw_step", _p(t["params"]), _p(t["grads"]), _p(t["exp_avg"]), _p(t["exp_avg_sq"]), _p(t["sizes"]),
-                      _p(t["wd"]), _p(t["chunk_tensor"]), _p(t["chunk_offset"]), t["n_chunks"], lr, b1, b2, eps, step,
-                      _stream(v[0][0]))
+            K.adamw_step(t["params"], t["grads"], t["exp_avg"], t["exp_avg_sq"], t["sizes"], t["wd"], t["chunk_tensor"],
+                         t["chunk_offset"], t["n_chunks"], lr, b1, b2, eps, step)
         return loss
 
 
 def clamp_logit_scale(logit_scale, lo=0.0, hi=4.6052):
     """scripts/main_lavila_pretrain.py:880 on the device (no host synchronisation)."""
-    _lib.call("avn_clamp_scalar_f32", _p(logit_scale.data), float(lo), float(hi), _stream(logit_scale.data))
+    K.clamp_scalar_f32(logit_scale.data, float(lo), float(hi))

@@ -31,12 +31,24 @@ int avn_sample_rrc_boxes(uint64_t seed, int n, int src_w, int src_h, double scal
 /* ---- T1+T2: fused uint8 -> bf16 crop / normalise / patchify ---------------------------------------------------
  * Replaces frames.astype(float32) (avion/data/clip_dataset.py:104,164), permute + kornia Normalize
  * (scripts/main_lavila_pretrain.py:816-817) and the einops patchify (avion/models/transformer.py:319) in one pass.
- * frames: u8 [B][T][Hs][Ws][3]; boxes: device int32 [B][3] = (x, y, hflip) or NULL (x=y=0, no flip);
+ * frames: u8 [B][T][Hs][Ws][3]; boxes: device int32 [B][3] = (x, y, hflip) or NULL (x=y=0, no flip); x, y are clamped
+ * into [0, Ws-crop] x [0, Hs-crop] (ffmpeg's crop filter does the same with decord's off-by-one upper bound);
  * patches: bf16 [B][T*gh*gw][F], F = 3*patch*patch rounded up to a multiple of 8 (zero padding; 588 -> 592 for ViT-L/14),
  * token = t*gh*gw + hh*gw + ww, feature = c*p*p + sh*p + sw. */
 int avn_clip_transform_u8_bf16(const uint8_t* frames, void* patches, int B, int T, int Hs, int Ws, int crop, int patch,
                                const int32_t* boxes, const float* mean3 /* host */, const float* std3 /* host */,
                                avn_stream_t stream);
+
+/* Same output contract, but each clip's crop box (x, y, w, h) is RESIZED to crop x crop: the "scale=W:H" stage of decord's
+ * fused filter graph "crop=w:h:x:y,[hflip,]scale=W:H" (threaded_decoder.cc:92) and the non-fused path's
+ * torchvision RandomResizedCrop (scripts/main_lavila_pretrain.py:437-441).  boxes: device int32 [B][5] = (x, y, w, h, hflip),
+ * the layout avn_sample_rrc_boxes writes; offsets are clamped into the frame like ffmpeg's crop filter does.  Filter:
+ * separable antialiased bilinear (torch _upsample_bilinear2d_aa, support max(scale, 1)) on the uint8 values, rounded to the
+ * uint8 grid (what the reference's decoder hands over), then (x - mean) / std.  swscale's own kernel has no source in the
+ * AVION tree: pixel parity with decord after a resize is unpinned; parity is against torchvision's resized_crop. */
+int avn_clip_resize_transform_u8_bf16(const uint8_t* frames, void* patches, int B, int T, int Hs, int Ws, int crop, int patch,
+                                      const int32_t* boxes, const float* mean3 /* host */, const float* std3 /* host */,
+                                      avn_stream_t stream);
 
 /* ---- V3: LayerNorm (nn.LayerNorm / LayerNorm subclass, avion/models/transformer.py:35-41,213) ------------------
  * x,y bf16 [rows][D]; gamma,beta fp32 [D]; mean,rstd fp32 [rows] (saved for backward; may be NULL in fwd). */
@@ -125,16 +137,18 @@ int avn_head_bwd(const float* demb, const void* x, const int64_t* row_idx, const
 
 /* ---- L2: sharded InfoNCE (ClipLoss, avion/losses/losses.py:103-149, local rows x gathered columns) -------------
  * img,txt fp32 [n][E] local rows; all_img, all_txt fp32 [N][E] gathered; labels = row_offset + r.
+ * scale: DEVICE pointer to one fp32 (logit_scale.exp(), model_clip.py:98) - read by the kernel, never by the host.
  * out[0] += sum over local rows of (CE_i + CE_t)/2, out[1] += number of correct image->text argmaxes.
  * lse fp32 [2][n] saved for backward. */
-int avn_infonce_fwd(const float* img, const float* txt, const float* all_img, const float* all_txt, float scale,
+int avn_infonce_fwd(const float* img, const float* txt, const float* all_img, const float* all_txt, const float* scale,
                     int n, int N, int E, int row_offset, float* lse, float* out, avn_stream_t stream);
-/* gscale = dLoss/d(mean local loss).  Produces d_all [2][N][E] fp32 (+=; image block first, then text; contains
- * the column-side gradients and, at rows row_offset.., the local row-side gradients) and dscale[1] (+=).
- * dlogits workspace fp32 [2][n][N]. */
-int avn_infonce_bwd(const float* img, const float* txt, const float* all_img, const float* all_txt, float scale,
-                    int n, int N, int E, int row_offset, const float* lse, float gscale, float* dlogits, float* d_all,
-                    float* dscale, avn_stream_t stream);
+/* gscale = dLoss/d(mean local loss).  Produces d_all [2][N][E] fp32 (+=; image block first, then text; contains,
+ * at rows row_offset.., the local row-side gradients and - when col_side != 0 - the column-side gradients of every
+ * gathered row) and dscale[1] (+=).  col_side = 0 is the reference's local_loss=True, gather_with_grad=False mode, whose
+ * gathered copies carry no gradient (losses.py:61-72).  dlogits workspace fp32 [2][n][N]. */
+int avn_infonce_bwd(const float* img, const float* txt, const float* all_img, const float* all_txt, const float* scale,
+                    int n, int N, int E, int row_offset, const float* lse, float gscale, int col_side, float* dlogits,
+                    float* d_all, float* dscale, avn_stream_t stream);
 
 /* ---- O1: optimizer step (scripts/main_lavila_pretrain.py:296-341 AdamW with weight-decay / no-decay groups; :880 clamp) --
  * One launch updates every tensor: device tables of n tensors (params, grads, exp_avg, exp_avg_sq: fp32 pointers; sizes in

@@ -161,6 +161,52 @@ def crop_clip(frames_u8: torch.Tensor, boxes, out_hw) -> torch.Tensor:
     return torch.stack(out)
 
 
+def _aa_weights(in_size: int, out_size: int) -> torch.Tensor:
+    """Dense [out_size, in_size] fp32 weight matrix of torch's antialiased bilinear resize
+    (aten/src/ATen/native/cpu/UpSampleKernel.cpp, HelperInterpBase::_compute_indices_min_size_weights_aa with the triangle
+    filter; align_corners=False): centre = scale (i + 0.5), support = max(scale, 1), taps
+    [max(0, int(centre - support + 0.5)), min(in, int(centre + support + 0.5))), weight 1 - |(j - centre + 0.5) / max(scale, 1)|
+    clipped at 0 and normalised by their sum.  All arithmetic in fp32 like the float kernel."""
+    f32 = np.float32
+    scale = f32(in_size) / f32(out_size)
+    support = scale if scale >= 1 else f32(1)
+    inv = f32(1) / scale if scale >= 1 else f32(1)
+    W = np.zeros((out_size, in_size), dtype=np.float32)
+    for i in range(out_size):
+        c = scale * (f32(i) + f32(0.5))
+        lo = max(int(c - support + f32(0.5)), 0)
+        hi = min(int(c + support + f32(0.5)), in_size)
+        j = np.arange(lo, hi, dtype=np.float32)
+        w = np.maximum(f32(0), f32(1) - np.abs((j - c + f32(0.5)) * inv)).astype(np.float32)
+        W[i, lo:hi] = w / w.sum(dtype=np.float32)
+    return torch.from_numpy(W)
+
+
+def resized_crop_clip(frames_u8: torch.Tensor, boxes, out_hw) -> torch.Tensor:
+    """Random-RESIZED crop per clip: box (x, y, w, h, hflip) of each clip -> crop -> hflip -> resize to out_hw -> uint8.
+    Order of decord's filter graph 'crop=w:h:x:y,[hflip,]scale=W:H' (third_party/decord/src/video/ffmpeg/threaded_decoder.cc:92);
+    the offsets are clamped into the frame as ffmpeg's crop filter does (the sampler's upper bound is one too large, :66-67).
+    The resize itself restates torchvision's RandomResizedCrop of the non-fused path (scripts/main_lavila_pretrain.py:437-441):
+    bilinear with antialiasing (float kernel), rounded half-to-even and clamped to uint8.  swscale (what decord really
+    calls) has no source in the tree: PARITY UNPINNED against decord pixels; pinned against torch.nn.functional.interpolate
+    and torchvision.transforms.v2.functional.resized_crop in tests/test_oracle.py."""
+    B, T, Hs, Ws, _ = frames_u8.shape
+    H, W = out_hw
+    out = torch.empty(B, T, H, W, 3, dtype=torch.uint8)
+    for b in range(B):
+        x, y, w, h, flip = (int(v) for v in boxes[b])
+        w, h = min(max(w, 1), Ws), min(max(h, 1), Hs)
+        x, y = min(max(x, 0), Ws - w), min(max(y, 0), Hs - h)
+        c = frames_u8[b, :, y:y + h, x:x + w, :].to(torch.float32)          # [T,h,w,3]
+        if flip:
+            c = torch.flip(c, dims=[2])
+        Wx, Wy = _aa_weights(w, W), _aa_weights(h, H)
+        hz = torch.einsum("ow,thwc->thoc", Wx, c)                            # horizontal pass first, like the aten kernel
+        r = torch.einsum("ph,thoc->tpoc", Wy, hz)
+        out[b] = r.round().clamp_(0, 255).to(torch.uint8)
+    return out
+
+
 def clip_transform(frames_u8: torch.Tensor, mean=MEAN_OPENAI, std=STD_OPENAI) -> torch.Tensor:
     """uint8 [B,T,H,W,3] -> f32 [B,3,T,H,W] normalised.
     astype(float32): avion/data/clip_dataset.py:104,164; permute: scripts/main_lavila_pretrain.py:816;
@@ -295,6 +341,51 @@ def clip_loss_local(img, txt, all_img, all_txt, scale, rank):
     loss = (F.cross_entropy(logits_i, labels) + F.cross_entropy(logits_t, labels)) / 2
     acc = 100 * (logits_i.argmax(-1) == labels).sum() / n
     return {"loss": loss, "clip_acc": acc}
+
+
+def clip_loss_world(imgs, txts, scale, local_loss: bool, gather_with_grad: bool):
+    """Single-process restatement of ClipLoss over W ranks for every (local_loss, gather_with_grad) mode
+    (gather_features, avion/losses/losses.py:53-75, non-horovod branch; loss :103-149).
+
+    imgs, txts: lists (one entry per rank) of leaf tensors [n,E]; scale: leaf scalar.  Returns one dict per rank with that
+    rank's `loss`, `clip_acc` and the gradients its backward() leaves on ITS OWN inputs before DDP averages parameters:
+    `dimg`, `dtxt` (what reaches image_features / text_features of rank r, including - with gather_with_grad - the
+    reduce-scatter of every other rank's contribution, torch.distributed.nn.all_gather backward) and `dscale`
+    (rank r's own d loss_r / d scale).  Pinned against the live reference under gloo in tests/test_oracle.py."""
+    W = len(imgs)
+    n = imgs[0].shape[0]
+    outs, losses = [], []
+    feat_grads = [[torch.zeros_like(imgs[r]), torch.zeros_like(txts[r])] for r in range(W)]
+    for r in range(W):
+        if gather_with_grad:                      # :55-60: differentiable gather, gradient flows to every rank's features
+            g_img, g_txt = list(imgs), list(txts)
+        else:                                     # :62-72: plain all_gather, copies carry no gradient ...
+            g_img = [t.detach() for t in imgs]
+            g_txt = [t.detach() for t in txts]
+            if not local_loss:                    # ... unless the own slice is put back (:68-72)
+                g_img[r], g_txt[r] = imgs[r], txts[r]
+        all_img, all_txt = torch.cat(g_img), torch.cat(g_txt)
+        if local_loss:                            # :116-118
+            logits_i = scale * imgs[r] @ all_txt.T
+            logits_t = scale * txts[r] @ all_img.T
+            labels = torch.arange(n) + n * r      # :132-133
+        else:                                     # :119-123
+            logits_i = scale * all_img @ all_txt.T
+            logits_t = logits_i.T
+            labels = torch.arange(W * n)
+        loss = (F.cross_entropy(logits_i, labels) + F.cross_entropy(logits_t, labels)) / 2
+        acc = 100 * (logits_i.argmax(-1) == labels).sum() / logits_i.shape[0]
+        leaves = list(imgs) + list(txts) + [scale]
+        grads = torch.autograd.grad(loss, leaves, allow_unused=True)
+        for q in range(W):                        # rank r's backward sends these to rank q (all_gather backward sums them)
+            if grads[q] is not None:
+                feat_grads[q][0] += grads[q]
+            if grads[W + q] is not None:
+                feat_grads[q][1] += grads[W + q]
+        outs.append({"loss": loss.detach(), "clip_acc": acc, "dscale": grads[-1]})
+    for r in range(W):
+        outs[r]["dimg"], outs[r]["dtxt"] = feat_grads[r]
+    return outs
 
 
 def train_step_forward(sd, clips_u8, tokens, cfg: ClipCfg):

@@ -115,3 +115,83 @@ def test_max_margin_rank_routing_gloo_world2():
         p.join(timeout=120)
         assert p.exitcode == 0
     assert dict(q.get(timeout=5) for _ in range(world)) == {0: True, 1: True}
+
+
+# ---- all four gather_features modes through avion_b200.losses.ClipLoss (host logic) -------------------------------------
+def _cpu_infonce_kernels():
+    """CPU stand-ins with the SEMANTICS of avn_infonce_fwd / avn_infonce_bwd (include/avion_b200.h): rank-local rows against
+    the gathered columns; d_all [2,N,E] = row-side gradient at rows row_offset.. plus, if col_side, the column-side gradient
+    of every gathered row.  Only the routing around them (avion_b200/losses/losses.py, _dist.py) is under test here."""
+    import torch.nn.functional as F
+
+    def fwd(img, txt, all_img, all_txt, scale, off):
+        n = img.shape[0]
+        li, lt = scale * img @ all_txt.T, scale * txt @ all_img.T
+        labels = torch.arange(n) + off
+        lse = torch.stack([torch.logsumexp(li, -1), torch.logsumexp(lt, -1)])
+        loss_sum = 0.5 * (F.cross_entropy(li, labels, reduction="sum") + F.cross_entropy(lt, labels, reduction="sum"))
+        correct = (li.argmax(-1) == labels).sum().float()
+        return lse, torch.stack([loss_sum, correct])
+
+    def bwd(img, txt, all_img, all_txt, scale, off, lse, gscale, col_side=True):
+        n, N = img.shape[0], all_img.shape[0]
+        i_, t_ = img.clone().requires_grad_(True), txt.clone().requires_grad_(True)
+        ai, at = all_img.clone().requires_grad_(True), all_txt.clone().requires_grad_(True)
+        sc = scale.clone().requires_grad_(True)
+        labels = torch.arange(n) + off
+        with torch.enable_grad():
+            loss = gscale * 0.5 * (F.cross_entropy(sc * i_ @ at.T, labels) + F.cross_entropy(sc * t_ @ ai.T, labels))
+            gi, gt, gai, gat, gs = torch.autograd.grad(loss, [i_, t_, ai, at, sc])
+        d_all = torch.zeros(2, N, img.shape[1])
+        d_all[0, off:off + n] += gi
+        d_all[1, off:off + n] += gt
+        if col_side:
+            d_all[0] += gai
+            d_all[1] += gat
+        return d_all, gs.reshape(1)
+
+    return fwd, bwd
+
+
+def _worker_modes(rank, world, port, q):
+    sys.path.insert(0, ROOT)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from avion_b200 import ops
+        from avion_b200.losses import ClipLoss
+        from oracle import cliploss_modes as M
+        ops.infonce_fwd, ops.infonce_bwd = _cpu_infonce_kernels()
+        n, E, scale = 5, 16, 9.0
+        g_img, g_txt = M.features(n, E, world, 11)
+        off = rank * n
+        bad = []
+        for ll, gwg in M.MODES:
+            img = g_img[off:off + n].clone().requires_grad_(True)
+            txt = g_txt[off:off + n].clone().requires_grad_(True)
+            sc = torch.tensor(scale, requires_grad=True)
+            out = ClipLoss(local_loss=ll, gather_with_grad=gwg, rank=rank, world_size=world)(img, txt, sc)
+            out["loss"].backward()
+            ref = M.oracle_world(g_img, g_txt, scale, n, world, ll, gwg)[rank]
+            bad += [f"local_loss={ll} gather_with_grad={gwg}: {b}" for b in M.check_rank(out, (img.grad, txt.grad, sc.grad), ref)]
+        q.put((rank, bad))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_clip_loss_all_gather_modes_gloo_world2():
+    """ClipLoss(local_loss, gather_with_grad) for all four combinations == the oracle's restatement of gather_features +
+    ClipLoss (pinned to the reference by tests/golden/cliploss_modes_w2.npz): loss, accuracy, feature gradients and the
+    logit-scale gradient of each rank."""
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29700 + (os.getpid() % 100)
+    procs = [ctx.Process(target=_worker_modes, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    res = dict(q.get(timeout=5) for _ in range(world))
+    assert res == {0: [], 1: []}, res

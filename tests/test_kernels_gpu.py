@@ -66,6 +66,59 @@ def test_clip_transform_crop_flip_bit_exact(ops):
     assert torch.equal(got.cpu(), ref)
 
 
+def test_clip_transform_clamps_boxes_and_takes_any_alignment(ops):
+    """Offsets one past the last valid position (decord's sampler draws x in [0, W-w+1], threaded_decoder.cc:66-67) are clamped
+    into the frame like ffmpeg's crop filter does - the kernel never reads a neighbouring row.  A frames pointer that is not
+    16-byte aligned exercises the bulk-load alignment logic and the guarded copy of the buffer's first / last row."""
+    from avion_b200.data.transforms import MEAN_TIMM, STD_TIMM
+    B, T, Hs, Ws, crop, p = 2, 2, 70, 90, 64, 16
+    clips = torch.from_numpy(np.random.RandomState(5).randint(0, 256, (B, T, Hs, Ws, 3)).astype(np.uint8))
+    edge = torch.tensor([[26, 6, 0], [26, 6, 1]], dtype=torch.int32)
+    past = torch.tensor([[27, 7, 0], [400, 99, 1]], dtype=torch.int32)
+    ref = O.patchify(O.clip_transform(O.crop_clip(clips, edge, (crop, crop))), p).to(bf16)
+    assert torch.equal(ops.clip_transform(clips.cuda(), crop, p, O.MEAN_OPENAI, O.STD_OPENAI, boxes=past.cuda()).cpu(), ref)
+    for shift in (1, 5, 15):
+        buf = torch.zeros(clips.numel() + 16, dtype=torch.uint8, device="cuda")
+        view = buf[shift:shift + clips.numel()].view(clips.shape)
+        view.copy_(clips)
+        assert view.data_ptr() % 16 == shift and view.is_contiguous()
+        assert torch.equal(ops.clip_transform(view, crop, p, O.MEAN_OPENAI, O.STD_OPENAI, boxes=edge.cuda()).cpu(), ref)
+    # another mean / std pair (timm style): still bit-exact bf16((x - mean) / std)
+    ref_t = O.patchify(O.clip_transform(O.crop_clip(clips, edge, (crop, crop)), MEAN_TIMM, STD_TIMM), p).to(bf16)
+    assert torch.equal(ops.clip_transform(clips.cuda(), crop, p, MEAN_TIMM, STD_TIMM, boxes=edge.cuda()).cpu(), ref_t)
+
+
+@pytest.mark.parametrize("case", ["down16", "mixed16", "patch14"])
+def test_clip_resize_transform_matches_oracle(ops, case):
+    """Fused crop -> hflip -> resize -> normalise -> patchify (decord 'crop=..,hflip,scale=..', threaded_decoder.cc:92) against the
+    oracle's restatement of torchvision's antialiased-bilinear resized_crop: box arithmetic and patch order exact, pixel values
+    equal to bf16(normalise(oracle uint8)) except where an fp32 summation-order difference crosses a rounding tie (then one
+    grey level apart).  swscale parity is unpinned (no source in the tree)."""
+    if case == "patch14":
+        B, T, Hs, Ws, crop, p = 2, 2, 90, 130, 56, 14
+        boxes = torch.tensor([[3, 4, 120, 80, 0], [40, 10, 33, 47, 1]], dtype=torch.int32)
+    elif case == "down16":
+        B, T, Hs, Ws, crop, p = 2, 3, 288, 384, 224, 16
+        boxes = torch.tensor([[10, 20, 300, 260, 0], [0, 0, 384, 288, 1]], dtype=torch.int32)
+    else:
+        B, T, Hs, Ws, crop, p = 4, 2, 101, 157, 64, 16
+        boxes = torch.tensor([[0, 0, 157, 101, 0], [93, 37, 64, 64, 1], [5, 11, 40, 30, 0], [58, 2, 100, 100, 1]], dtype=torch.int32)
+    clips = torch.from_numpy(np.random.RandomState(7).randint(0, 256, (B, T, Hs, Ws, 3)).astype(np.uint8))
+    u8 = O.resized_crop_clip(clips, boxes, (crop, crop))
+    ref = O.patchify(O.clip_transform(u8), p)
+    got = ops.clip_resize_transform(clips.cuda(), boxes.cuda(), crop, p, O.MEAN_OPENAI, O.STD_OPENAI).cpu()
+    feat = 3 * p * p
+    assert got.shape[-1] == (feat + 7) // 8 * 8 and torch.count_nonzero(got[..., feat:]) == 0
+    got = got[..., :feat].float()
+    same = got == ref.to(bf16).float()
+    assert same.float().mean() > 0.999, float(same.float().mean())
+    one_level = 1.0 / min(O.STD_OPENAI) + 2.0 ** -6
+    assert float((got - ref).abs().max()) <= one_level
+    if case == "mixed16":      # a box of exactly the output size is a plain crop (+ flip): bit-exact with the crop kernel
+        plain = ops.clip_transform(clips.cuda(), crop, p, O.MEAN_OPENAI, O.STD_OPENAI, boxes=torch.tensor([[0, 0, 0], [93, 37, 1], [0, 0, 0], [0, 0, 0]], dtype=torch.int32).cuda())
+        assert torch.equal(plain[1].cpu().float(), got[1])
+
+
 @pytest.mark.parametrize("rows,D", [(1000, 768), (77 * 3, 512), (65 * 6, 128), (50, 1024)])
 def test_layernorm_fwd_bwd(ops, rows, D):
     x = rnd(rows, D, seed=1)
@@ -258,13 +311,25 @@ def test_infonce_fwd_bwd(ops, n, N, E, off):
     loss = (F.cross_entropy(li, labels) + F.cross_entropy(lt, labels)) / 2
     correct = (li.argmax(-1) == labels).sum()
     loss.backward()
-    lse, out = ops.infonce_fwd(all_img[off:off + n].contiguous(), all_txt[off:off + n].contiguous(), all_img, all_txt, scale, off)
+    scale_dev = torch.full((1,), scale, device="cuda")          # the kernels read logit_scale.exp() from device memory
+    lse, out = ops.infonce_fwd(all_img[off:off + n].contiguous(), all_txt[off:off + n].contiguous(), all_img, all_txt, scale_dev, off)
     assert abs(float(out[0]) / n - float(loss)) < 1e-4 * max(1.0, abs(float(loss)))
     assert int(out[1]) == int(correct)
-    d_all, dscale = ops.infonce_bwd(all_img[off:off + n].contiguous(), all_txt[off:off + n].contiguous(), all_img, all_txt, scale,
+    d_all, dscale = ops.infonce_bwd(all_img[off:off + n].contiguous(), all_txt[off:off + n].contiguous(), all_img, all_txt, scale_dev,
                                     off, lse, 1.0)
     assert rel_err(d_all[0], ai.grad) < 1e-4 and rel_err(d_all[1], at.grad) < 1e-4
     assert abs(float(dscale) - float(sc.grad)) < 1e-4 * max(1.0, abs(float(sc.grad)))
+    # col_side=False (local_loss without gather_with_grad, losses.py:61-72): the gathered operands are constants, so only the
+    # direct use of the local rows is differentiated
+    ci, ct = all_img[off:off + n].clone().requires_grad_(True), all_txt[off:off + n].clone().requires_grad_(True)
+    l2 = (F.cross_entropy(scale * ci @ all_txt.T, labels) + F.cross_entropy(scale * ct @ all_img.T, labels)) / 2
+    l2.backward()
+    d_rows, _ = ops.infonce_bwd(all_img[off:off + n].contiguous(), all_txt[off:off + n].contiguous(), all_img, all_txt, scale_dev,
+                                off, lse, 1.0, col_side=False)
+    assert rel_err(d_rows[0, off:off + n], ci.grad) < 1e-4 and rel_err(d_rows[1, off:off + n], ct.grad) < 1e-4
+    mask = torch.ones(N, dtype=torch.bool, device="cuda")
+    mask[off:off + n] = False
+    assert float(d_rows[:, mask].abs().max()) == 0.0 if N > n else True
 
 
 def test_fused_adamw_matches_torch(ops):
