@@ -101,22 +101,32 @@ def _build(vision_kw, text_kw, project_embed_dim, freeze_temperature, use_grad_c
     text_model.set_grad_checkpointing(use_grad_checkpointing)
     model = CLIP(embed_dim=project_embed_dim, vision_model=vision_model, text_model=text_model,
                  freeze_temperature=freeze_temperature)
-    if pretrain_zoo in ("openai", "open_clip") and pretrain_path is not None:
-        # a checkpoint already remapped to the flash + fast_conv1 naming (avion/models/utils.py:15-98)
-        sd = torch.load(pretrain_path, map_location="cpu")
-        sd = sd.get("state_dict", sd)
-        sd = {k[len("module."):] if k.startswith("module.") else k: v for k, v in sd.items()}
-        missing, unexpected = model.load_state_dict(sd, strict=False)
-        print("missing_keys: ", missing)
-        print("unexpected_keys: ", unexpected)
-    elif pretrain_zoo not in (None, "none", "random"):
-        raise NotImplementedError("no network on this box: pass pretrain_zoo='random' or a local pretrain_path")
+    if pretrain_zoo in (None, "none", "random"):
+        return model                               # random init (this package's extension: the reference always loads)
+    if pretrain_zoo not in ("openai", "open_clip"):
+        raise NotImplementedError(pretrain_zoo)    # model_clip.py:175-176
+    if pretrain_path is None:
+        # 'openai' downloads through clip.load (model_clip.py:150-152); there is no network behind this package
+        raise NotImplementedError(f"pretrain_zoo={pretrain_zoo!r} needs pretrain_path=<local OpenAI / OpenCLIP state dict> "
+                                  "(no download here); pass pretrain_zoo='random' for random init")
+    # model_clip.py:150-174: OpenAI / OpenCLIP key names -> the flash + fast_conv1 names of this package
+    from .utils import remap_keys_from_open_clip_to_vit
+    print("=> loading {} model".format(pretrain_zoo))
+    state_dict = torch.load(pretrain_path, map_location="cpu")
+    if hasattr(state_dict, "state_dict"):          # a pickled OpenAI CLIP module
+        state_dict = state_dict.state_dict()
+    remapped = remap_keys_from_open_clip_to_vit(state_dict, len(vision_model.transformer.resblocks), len(text_model.transformer.resblocks),
+                                                context_length=text_model.context_length, vocab_size=text_model.vocab_size,
+                                                use_fast_conv1=True, use_flash_attn=True)
+    missing, unexpected = model.load_state_dict(remapped, strict=False)
+    print("missing_keys: ", missing)
+    print("unexpected_keys: ", unexpected)
     return model
 
 
 def CLIP_VITB16(freeze_temperature=False, use_grad_checkpointing=False, use_bidirectional_lm=False, context_length=77,
                 patch_dropout=0.0, drop_path_rate=0.0, num_frames=1, use_fast_conv1=True, use_flash_attn=True,
-                project_embed_dim=512, pretrain_zoo="random", pretrain_path=None, **kwargs):
+                project_embed_dim=512, pretrain_zoo="openai", pretrain_path=None, **kwargs):
     """avion/models/model_clip.py:102-177 (ViT-B/16 video tower + 12L/512 text tower)."""
     return _build(dict(image_size=224, patch_size=16, width=768, layers=12, heads=12, mlp_ratio=4, patch_dropout=patch_dropout,
                        drop_path_rate=drop_path_rate, num_frames=num_frames),
@@ -127,7 +137,7 @@ def CLIP_VITB16(freeze_temperature=False, use_grad_checkpointing=False, use_bidi
 
 def CLIP_VITL14(freeze_temperature=False, use_grad_checkpointing=False, use_bidirectional_lm=False, context_length=77,
                 vocab_size=49408, patch_dropout=0.0, drop_path_rate=0.0, num_frames=1, use_fast_conv1=True, use_flash_attn=True,
-                project_embed_dim=512, pretrain_zoo="random", pretrain_path=None, **kwargs):
+                project_embed_dim=512, pretrain_zoo="openai", pretrain_path=None, **kwargs):
     """avion/models/model_clip.py:180-259 (ViT-L/14 video tower: 24 blocks, width 1024, 16 heads; 12L/768 text tower).
     Patch 14: token rows are 588 features padded to 592 (16-byte rows); conv1.weight keeps the reference shape [1024, 588]."""
     return _build(dict(image_size=224, patch_size=14, width=1024, layers=24, heads=16, mlp_ratio=4, patch_dropout=patch_dropout,

@@ -16,7 +16,16 @@ class FusedAdamW(torch.optim.Optimizer):
         if lr < 0 or eps < 0 or not (0 <= betas[0] < 1) or not (0 <= betas[1] < 1) or weight_decay < 0:
             raise ValueError("invalid AdamW hyper-parameters")
         super().__init__(params, dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay))
-        self._tables = None      # (key, device tables) rebuilt when the set of tensors with gradients changes
+        self._tables = None      # {(device, pointer signature): device tables}; rebuilt only when the set of tensors changes
+
+    def load_state_dict(self, state_dict):
+        """Checkpoints of torch's fused / capturable AdamW keep `step` as a CUDA tensor; reading it every step would cost one
+        host synchronisation per parameter, so the step counters come back to the host once, here."""
+        super().load_state_dict(state_dict)
+        for st in self.state.values():
+            if torch.is_tensor(st.get("step")) and st["step"].is_cuda:
+                st["step"] = st["step"].detach().float().cpu()
+        self._tables = None
 
     def _build_tables(self, entries, dev):
         chunk = _lib.load().avn_adamw_chunk_elems()
@@ -58,15 +67,23 @@ class FusedAdamW(torch.optim.Optimizer):
                 key = (float(group["lr"]), float(group["betas"][0]), float(group["betas"][1]), float(group["eps"]),
                        int(st["step"]), p.device)
                 launches.setdefault(key, []).append((p, p.grad, st["exp_avg"], st["exp_avg_sq"], float(group["weight_decay"])))
-        sig = tuple((k, tuple((e[0].data_ptr(), e[1].data_ptr(), e[2].data_ptr(), e[3].data_ptr(), e[4]) for e in v))
-                    for k, v in launches.items())
-        if self._tables is None or self._tables[0] != tuple((k[:4] + k[5:], s) for k, s in sig):
+        # Device tables depend only on WHICH tensors go out together (pointers, weight decay) - not on lr / betas / eps / step,
+        # which are launch arguments: a per-iteration lr schedule (main_lavila_pretrain.py:805-808) must not rebuild them.
+        if self._tables is None:
+            self._tables = {}
+        tables = {}
+        for k, v in launches.items():
+            sig = (k[5], tuple((e[0].data_ptr(), e[1].data_ptr(), e[2].data_ptr(), e[3].data_ptr(), e[4]) for e in v))
             # (gradient buffers are stable under DDP's gradient_as_bucket_view and zero_grad(set_to_none=False); with
             # set_to_none=True PyTorch's caching allocator normally hands the same blocks back - otherwise this rebuilds)
-            self._tables = (tuple((k[:4] + k[5:], s) for k, s in sig),
-                            {k[:4] + k[5:]: self._build_tables(v, k[5]) for k, v in launches.items()})
+            t = self._tables.get(sig)
+            if t is None:
+                if len(self._tables) > 8:
+                    self._tables.clear()
+                t = self._tables[sig] = self._build_tables(v, k[5])
+            tables[k] = t
         for k, v in launches.items():
-            t = self._tables[1][k[:4] + k[5:]]
+            t = tables[k]
             lr, b1, b2, eps, step, dev = k
             K.adamw_step(t["params"], t["grads"], t["exp_avg"], t["exp_avg_sq"], t["sizes"], t["wd"], t["chunk_tensor"],
                          t["chunk_offset"], t["n_chunks"], lr, b1, b2, eps, step)

@@ -15,7 +15,7 @@ def run():
     from avion_b200.losses import ClipLoss
 
     assert torch.cuda.is_available(), "smoke() needs a CUDA device"
-    cfg, B = O.TINY, 6
+    cfg, B = O.TINY, 32
     sd = O.make_state_dict(cfg, 0)
     clips, tokens = O.make_inputs(cfg, B, 1234)
     model = build_model(cfg).cuda()
@@ -33,7 +33,7 @@ def run():
     print(f"smoke: loss={out['loss'].item():.5f} oracle={ref['loss'].item():.5f} rel={rel:.2e} cos_img={cos_i:.5f} cos_txt={cos_t:.5f} "
           f"|dconv1|={gn:.3e}")
     assert cos_i >= 0.999 and cos_t >= 0.999, "embedding cosine below 0.999"
-    assert rel < 1e-3 * 5, "loss deviates from the oracle"
+    assert rel < 1e-3, "loss deviates from the oracle by more than 1e-3 (north-star tolerance)"
     assert gn > 0 and gn == gn
     run_videomae()
 

@@ -1,6 +1,7 @@
-"""Import the UNMODIFIED reference (/root/reference/avion) on CPU.  TEST INFRASTRUCTURE ONLY.
+"""Import the UNMODIFIED reference (/root/reference/avion, or its staged copy oracle/_ref/avion).  TEST INFRASTRUCTURE ONLY.
 
-Works only in the build container (the GPU box has no /root/reference).  Two absent packages are shimmed
+/root/reference exists only in the build container; oracle/stage_ref.py stages the path's files byte for byte into the
+git-ignored oracle/_ref/ so that the GPU box can import them too.  Two absent packages are shimmed
 (SURVEY.md section 8c): ``timm.models.layers`` (3 symbols; DropPath rates are 0 in every config) and ``clip``
 (only used to download OpenAI weights, avion/models/model_clip.py:150-152).  flash-attn needs CUDA to execute,
 so the reference is built with use_flash_attn=False: same math, nn.MultiheadAttention naming; the bijection to
@@ -12,11 +13,18 @@ import types
 
 import torch
 
-REFERENCE_ROOT = "/root/reference"
+LIVE_ROOT = "/root/reference"
+STAGED_ROOT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")
+REFERENCE_ROOT = LIVE_ROOT if os.path.isdir(os.path.join(LIVE_ROOT, "avion")) else STAGED_ROOT
 
 
 def available() -> bool:
-    return os.path.isdir(os.path.join(REFERENCE_ROOT, "avion"))
+    return os.path.isfile(os.path.join(REFERENCE_ROOT, "avion", "models", "transformer.py"))
+
+
+def live() -> bool:
+    """True in the build container (the whole reference tree), False when only the staged files exist."""
+    return REFERENCE_ROOT == LIVE_ROOT
 
 
 def import_reference():
@@ -50,16 +58,18 @@ def to_reference_key(k: str) -> str:
     return k
 
 
-def build_reference_clip(cfg, sd):
-    """Reference CLIP built with the factory's literal arguments (model_clip.py:118-148) and loaded with sd."""
+def build_reference_clip(cfg, sd, use_flash_attn=False):
+    """Reference CLIP built with the factory's literal arguments (model_clip.py:118-148) and loaded with sd.
+    use_flash_attn=True (CUDA only) takes sd's flash naming as is; False maps it to the nn.MultiheadAttention naming."""
     VisionTransformer, TextTransformer, CLIP, _ = import_reference()
     vis = VisionTransformer(cfg.image_size, cfg.patch, cfg.width, cfg.layers, cfg.heads, 4,
                             output_dim=cfg.embed_dim, num_frames=cfg.frames,
-                            use_fast_conv1=True, use_flash_attn=False)
+                            use_fast_conv1=True, use_flash_attn=use_flash_attn)
     txt = TextTransformer(context_length=cfg.ctx, vocab_size=cfg.vocab, width=cfg.t_width, heads=cfg.t_heads,
                           layers=cfg.t_layers, output_dim=cfg.embed_dim, causal_mask=True)
     model = CLIP(embed_dim=cfg.embed_dim, vision_model=vis, text_model=txt)
-    missing, unexpected = model.load_state_dict({to_reference_key(k): v for k, v in sd.items()}, strict=True)
+    keyed = sd if use_flash_attn else {to_reference_key(k): v for k, v in sd.items()}
+    missing, unexpected = model.load_state_dict(keyed, strict=True)
     assert not missing and not unexpected
     return model.float()
 

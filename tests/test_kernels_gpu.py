@@ -119,7 +119,10 @@ def test_clip_resize_transform_matches_oracle(ops, case):
         assert torch.equal(plain[1].cpu().float(), got[1])
 
 
-@pytest.mark.parametrize("rows,D", [(1000, 768), (77 * 3, 512), (65 * 6, 128), (50, 1024)])
+# the last four give every persistent CTA several trips round its TMA ring (296 CTAs x 8 rows x up to 8 stages; 148 CTAs x 4
+# stages at D = 1024) and end in a ragged tile; (3, 384) has fewer rows than one tile
+@pytest.mark.parametrize("rows,D", [(1000, 768), (77 * 3, 512), (65 * 6, 128), (50, 1024), (3, 384), (25003, 768), (9001, 1024),
+                                    (40005, 384), (60001, 128)])
 def test_layernorm_fwd_bwd(ops, rows, D):
     x = rnd(rows, D, seed=1)
     g = (1 + 0.1 * torch.randn(D, device="cuda")).float()
@@ -137,6 +140,11 @@ def test_layernorm_fwd_bwd(ops, rows, D):
     assert rel_err(dx, xr.grad + dres.float()) < 5e-3
     assert rel_err(dg, gr.grad) < 2e-3 and rel_err(db, br.grad) < 2e-3
     assert rel_err(dc, dx.float().sum(0)) < 1e-4
+    assert rel_err(mean, x.float().mean(-1)) < 1e-5 and rel_err(rstd, (x.float().var(-1, unbiased=False) + 1e-6).rsqrt()) < 1e-5
+    # without the residual gradient / column sum (ln_pre's backward)
+    dg2, db2 = torch.zeros(D, device="cuda"), torch.zeros(D, device="cuda")
+    dx2 = ops.layernorm_bwd(dy, x, g, mean, rstd, dg2, db2)
+    assert rel_err(dx2, xr.grad) < 5e-3 and rel_err(dg2, gr.grad) < 2e-3
 
 
 # the last two are large enough for the CTA-pair (cta_group::2) kernels, with an odd number of ragged 128-row tiles
@@ -357,7 +365,23 @@ def test_fused_adamw_matches_torch(ops):
         assert torch.allclose(a, b, rtol=2e-6, atol=1e-7), float((a - b).abs().max())
     sd = o_our.state_dict()
     assert set(sd["state"][0].keys()) == {"step", "exp_avg", "exp_avg_sq"} and float(sd["state"][0]["step"]) == 5
-    o_ref.load_state_dict(sd)                        # checkpoints are interchangeable
+    import copy
+    o_ref.load_state_dict(copy.deepcopy(sd))         # checkpoints are interchangeable (deep copy: load_state_dict keeps same-device tensors by reference)
     ls = torch.nn.Parameter(torch.tensor(5.0, device="cuda"))
     clamp_logit_scale(ls)
     assert abs(float(ls) - 4.6052) < 1e-6
+    # an lr schedule changes lr every iteration (main_lavila_pretrain.py:805-808): the device tables must not be rebuilt
+    built = []
+    orig = o_our._build_tables
+    o_our._build_tables = lambda *a: (built.append(1), orig(*a))[1]
+    for step in range(3):
+        for grp_r, grp_o in zip(o_ref.param_groups, o_our.param_groups):
+            grp_r["lr"] = grp_o["lr"] = 3e-3 * (0.5 + 0.1 * step)
+        for a, b in zip(ref, ours):
+            b.grad.copy_(torch.randn_like(a))
+            a.grad.copy_(b.grad)
+        o_ref.step()
+        o_our.step()
+    assert not built
+    for a, b in zip(ref, ours):
+        assert torch.allclose(a, b, rtol=4e-6, atol=2e-7), float((a - b).abs().max())

@@ -132,3 +132,20 @@ def test_resized_crop_restatement_matches_torch_and_torchvision():
     # clamping of the sampler's off-by-one offsets (x + w == Ws + 1)
     far = O.resized_crop_clip(clips[:1], torch.tensor([[21, 17, 100, 80, 0]]), (64, 64))
     assert torch.equal(far, O.resized_crop_clip(clips[:1], torch.tensor([[20, 16, 100, 80, 0]]), (64, 64)))
+
+
+def test_bf16_point_oracle_without_points_is_the_fp32_oracle():
+    """oracle.bf16_points.Emu with no rounding point enabled is the fp32 oracle (to round-off): the rounding points are the only
+    thing it adds.  With all points it moves by the bf16 noise of the pipeline - for the tiny batch-6 fixture by more than the
+    1e-3 loss tolerance, which is the measured noise floor any bf16 implementation of this fixture lives with."""
+    from oracle.bf16_points import ALL_POINTS, Emu
+    g, cfg = load_golden("tiny_b6")
+    sd = O.make_state_dict(cfg, int(g["wseed"]))
+    clips, tokens = O.make_inputs(cfg, int(g["batch"]), int(g["iseed"]))
+    with torch.no_grad():
+        loss, img, txt = Emu(()).loss(sd, clips, tokens, cfg)
+        np.testing.assert_allclose(loss, float(g["loss"]), rtol=2e-6)
+        np.testing.assert_allclose(img.numpy(), g["image_embed"], rtol=1e-4, atol=2e-6)
+        noisy, img16, _ = Emu(ALL_POINTS).loss(sd, clips, tokens, cfg)
+    assert 1e-4 < abs(noisy - float(g["loss"])) / float(g["loss"]) < 1e-2
+    assert torch.nn.functional.cosine_similarity(img16, torch.from_numpy(g["image_embed"]), dim=-1).min() > 0.9995

@@ -85,3 +85,18 @@ if which in ("all", "ln"):
     dx = torch.empty_like(x)
     report("layernorm_bwd (+res,+colsum)", timeit(lambda: ops.layernorm_bwd(y, x, g, mean, rstd, dg, db, dres=x, dcolsum=dc, out=dx)), bytes_=8.0 * M * D)
     report("colsum 4D", timeit(lambda: ops.colsum(torch.empty(0, device=dev, dtype=bf) if False else x, dc)), bytes_=2.0 * M * D)
+
+if which in ("all", "transform"):
+    Hs, Ws = 288, 384
+    clips = torch.randint(0, 256, (B, 16, 224, 224, 3), dtype=torch.uint8, device=dev)
+    mean, std = (108.3272985, 116.7460125, 104.09373615000001), (68.5005327, 66.6321579, 70.32316305)
+    for p in (16, 14):
+        out = ops.clip_transform(clips, 224, p, mean, std)
+        report(f"clip_transform p={p}", timeit(lambda: ops.clip_transform(clips, 224, p, mean, std, out=out)), bytes_=float(clips.numel()) + 2.0 * out.numel())
+    nb = max(1, B // 2)
+    src = torch.randint(0, 256, (nb, 16, Hs, Ws, 3), dtype=torch.uint8, device=dev)
+    boxes = ops.sample_rrc_boxes(7, nb, Ws, Hs).to(dev)
+    out = ops.clip_resize_transform(src, boxes, 224, 16, mean, std)
+    area = float((boxes[:, 2] * boxes[:, 3]).sum()) * 16 * 3
+    report("clip_resize_transform p=16 (RRC 0.5-1.0 of 288x384)", timeit(lambda: ops.clip_resize_transform(src, boxes, 224, 16, mean, std, out=out)),
+           bytes_=area + 2.0 * out.numel())
