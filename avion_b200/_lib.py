@@ -6,7 +6,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "libavion_b200.so")
+# AVN_LIB_PATH: load another build of the same C-ABI (kernel A/B comparisons inside one GPU call; tools/ only)
+LIB_PATH = os.environ.get("AVN_LIB_PATH") or os.path.join(_HERE, "csrc", "libavion_b200.so")
 
 GEMM_NT, GEMM_NN, GEMM_TN = 0, 1, 2
 EPI_NONE, EPI_BIAS, EPI_BIAS_GELU, EPI_BIAS_GELU_DUAL, EPI_BIAS_RESIDUAL, EPI_DGELU, EPI_F32_ADD = range(7)
