@@ -72,7 +72,7 @@ ln_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ gam
         const long long tile = blockIdx.x + (long long)j * gridDim.x;
         if (tile >= n_tiles) return;
         const int s = j % stages;
-        mbar_wait(&ring.empty[s], ((j / stages) & 1) ^ 1);
+        mbar_wait_parked(&ring.empty[s], ((j / stages) & 1) ^ 1);
         if (elect_one()) {
             const long long r0 = tile * ROWS_PER_TILE;
             const uint32_t bytes = (uint32_t)(min((long long)ROWS_PER_TILE, rows - r0) * row_bytes);
@@ -84,69 +84,84 @@ ln_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ gam
     if (warp == 0)
         for (int j = 0; j < stages - 1; ++j) produce(j);
     // ===================== one row per warp =====================
-    // gamma / beta of this lane's columns stay in registers for all rows of the CTA
-    float g[VPL][8], bt[VPL][8];
+    // gamma / beta of this lane's columns stay in registers for all rows of the CTA (as f32x2 pairs: all the per-element
+    // arithmetic below is packed FADD2 / FMUL2 / FFMA2 - the kernel is bound by instruction issue, not by HBM, once the ring
+    // hides the load latency: 433 -> ~150 warp instructions per row)
+    float2 g[VPL][4], bt[VPL][4];
 #pragma unroll
     for (int j = 0; j < VPL; ++j) {
         const int i = lane + 32 * j;
 #pragma unroll
-        for (int e = 0; e < 8; ++e) { g[j][e] = 0.f; bt[j][e] = 0.f; }
+        for (int e = 0; e < 4; ++e) { g[j][e] = make_float2(0.f, 0.f); bt[j][e] = make_float2(0.f, 0.f); }
         if (i < nvec) {
             const float4 g0 = __ldg((const float4*)(gamma + i * 8)), g1 = __ldg((const float4*)(gamma + i * 8 + 4));
             const float4 b0 = __ldg((const float4*)(beta + i * 8)), b1 = __ldg((const float4*)(beta + i * 8 + 4));
-            g[j][0] = g0.x; g[j][1] = g0.y; g[j][2] = g0.z; g[j][3] = g0.w; g[j][4] = g1.x; g[j][5] = g1.y; g[j][6] = g1.z; g[j][7] = g1.w;
-            bt[j][0] = b0.x; bt[j][1] = b0.y; bt[j][2] = b0.z; bt[j][3] = b0.w; bt[j][4] = b1.x; bt[j][5] = b1.y; bt[j][6] = b1.z; bt[j][7] = b1.w;
+            g[j][0] = make_float2(g0.x, g0.y); g[j][1] = make_float2(g0.z, g0.w); g[j][2] = make_float2(g1.x, g1.y); g[j][3] = make_float2(g1.z, g1.w);
+            bt[j][0] = make_float2(b0.x, b0.y); bt[j][1] = make_float2(b0.z, b0.w); bt[j][2] = make_float2(b1.x, b1.y); bt[j][3] = make_float2(b1.z, b1.w);
         }
     }
+    const float inv_d = 1.0f / (float)D;
     int it = 0;
     for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
         const int s = it % stages;
         const long long row = tile * ROWS_PER_TILE + warp;
         if (warp == 0) produce(it + stages - 1);             // refills the slot every warp released in iteration it-1
-        mbar_wait(&ring.full[s], (it / stages) & 1);
-        float v[VPL][8];
-        float sum = 0.f;
+        mbar_wait_parked(&ring.full[s], (it / stages) & 1);
+        float2 v[VPL][4];
+        float2 acc[VPL];                                     // one accumulation chain per vector: independent FADD2 streams
         if (row < rows) {
             const uint8_t* xr = ring.data + s * ring.stage_bytes + warp * row_bytes;
 #pragma unroll
             for (int j = 0; j < VPL; ++j) {
                 const int i = lane + 32 * j;
+                acc[j] = make_float2(0.f, 0.f);
                 if (i < nvec) {
                     const uint4 u = lds128(xr + i * 16);
-                    const uint32_t w[4] = {u.x, u.y, u.z, u.w};
-#pragma unroll
-                    for (int e = 0; e < 4; ++e) { const float2 f = unpack_bf16(w[e]); v[j][2 * e] = f.x; v[j][2 * e + 1] = f.y; sum += f.x + f.y; }
+                    v[j][0] = unpack_bf16(u.x); v[j][1] = unpack_bf16(u.y); v[j][2] = unpack_bf16(u.z); v[j][3] = unpack_bf16(u.w);
+                    acc[j] = __fadd2_rn(__fadd2_rn(v[j][0], v[j][1]), __fadd2_rn(v[j][2], v[j][3]));
                 } else {
 #pragma unroll
-                    for (int e = 0; e < 8; ++e) v[j][e] = 0.f;
+                    for (int e = 0; e < 4; ++e) v[j][e] = make_float2(0.f, 0.f);
                 }
             }
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(&ring.empty[s]);          // the row is in registers: the slot can be refilled
         if (row >= rows) continue;
-        const float mean = warp_sum(sum) / D;
-        float q = 0.f;
+        float2 tot = acc[0];
 #pragma unroll
-        for (int j = 0; j < VPL; ++j)
+        for (int j = 1; j < VPL; ++j) tot = __fadd2_rn(tot, acc[j]);
+        const float mean = warp_sum(tot.x + tot.y) * inv_d;
+        const float2 nmean = make_float2(-mean, -mean);
+#pragma unroll
+        for (int j = 0; j < VPL; ++j) {                      // v <- v - mean (kept: the output needs it again), acc <- sum of squares
+            acc[j] = make_float2(0.f, 0.f);
             if (lane + 32 * j < nvec) {
 #pragma unroll
-                for (int e = 0; e < 8; ++e) { const float d = v[j][e] - mean; q += d * d; }
+                for (int e = 0; e < 4; ++e) { v[j][e] = __fadd2_rn(v[j][e], nmean); acc[j] = __ffma2_rn(v[j][e], v[j][e], acc[j]); }
             }
-        const float rstd = rsqrtf(warp_sum(q) / D + eps);
+        }
+        tot = acc[0];
+#pragma unroll
+        for (int j = 1; j < VPL; ++j) tot = __fadd2_rn(tot, acc[j]);
+        const float rstd = rsqrtf(warp_sum(tot.x + tot.y) * inv_d + eps);
         if (lane == 0) {
             if (mean_out) mean_out[row] = mean;
             if (rstd_out) rstd_out[row] = rstd;
         }
+        const float2 rs2 = make_float2(rstd, rstd);
         uint4* yr = (uint4*)(y + row * D);
 #pragma unroll
         for (int j = 0; j < VPL; ++j) {
             const int i = lane + 32 * j;
             if (i < nvec) {
-                float o[8];
+                uint32_t o[4];
 #pragma unroll
-                for (int e = 0; e < 8; ++e) o[e] = fmaf((v[j][e] - mean) * rstd, g[j][e], bt[j][e]);
-                yr[i] = make_uint4(pack_bf16(o[0], o[1]), pack_bf16(o[2], o[3]), pack_bf16(o[4], o[5]), pack_bf16(o[6], o[7]));
+                for (int e = 0; e < 4; ++e) {
+                    const float2 r = __ffma2_rn(__fmul2_rn(v[j][e], rs2), g[j][e], bt[j][e]);      // ((x - mean) * rstd) * g + b
+                    o[e] = pack_bf16(r.x, r.y);
+                }
+                yr[i] = make_uint4(o[0], o[1], o[2], o[3]);
             }
         }
     }
@@ -171,7 +186,7 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restr
         const long long tile = blockIdx.x + (long long)j * gridDim.x;
         if (tile >= n_tiles) return;
         const int s = j % stages;
-        mbar_wait(&ring.empty[s], ((j / stages) & 1) ^ 1);
+        mbar_wait_parked(&ring.empty[s], ((j / stages) & 1) ^ 1);
         if (elect_one()) {
             const long long r0 = tile * ROWS_PER_TILE;
             const uint32_t bytes = (uint32_t)(min((long long)ROWS_PER_TILE, rows - r0) * row_bytes);
@@ -199,19 +214,20 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restr
             float mean = 0.f, rstd = 0.f;
             if (row < rows) { mean = __ldg(mean_in + row); rstd = __ldg(rstd_in + row); }      // issued before the waits
             if (warp == 0) produce(it + stages - 1);
-            mbar_wait(&ring.full[s], (it / stages) & 1);
+            mbar_wait_parked(&ring.full[s], (it / stages) & 1);
             if (row < rows) {
                 const uint8_t* xr = ring.data + s * ring.stage_bytes + warp * row_bytes;
                 const uint8_t* dyr = xr + tens_bytes;
                 const uint8_t* drr = xr + 2 * tens_bytes;
                 // all the per-element arithmetic is packed f32x2 (FFMA2 / FADD2 / FMUL2)
                 const float2 rs2 = make_float2(rstd, rstd), nmr2 = make_float2(-mean * rstd, -mean * rstd);
-                float2 s1v = make_float2(0.f, 0.f), s2v = make_float2(0.f, 0.f);
+                float2 s1a[VPL], s2a[VPL];                    // one chain per vector (independent FADD2 / FFMA2 streams)
                 // x and dy are read from the staged tile in both passes (shared-memory bandwidth is idle here; keeping them in
                 // registers next to the 72 column accumulators spilled)
 #pragma unroll
                 for (int j = 0; j < VPL; ++j) {
                     const int i = lane + 32 * j;
+                    float2 s1v = make_float2(0.f, 0.f), s2v = make_float2(0.f, 0.f);
                     if (i < nvec) {
                         const uint4 ux = lds128(xr + i * 16), ud = lds128(dyr + i * 16);
                         const uint32_t wx[4] = {ux.x, ux.y, ux.z, ux.w}, wd[4] = {ud.x, ud.y, ud.z, ud.w};
@@ -230,8 +246,13 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restr
                             s2v = __ffma2_rn(t, h, s2v);
                         }
                     }
+                    s1a[j] = s1v; s2a[j] = s2v;
                 }
-                const float c1 = warp_sum(s1v.x + s1v.y) / D, c2 = warp_sum(s2v.x + s2v.y) / D;
+                float2 s1v = s1a[0], s2v = s2a[0];
+#pragma unroll
+                for (int j = 1; j < VPL; ++j) { s1v = __fadd2_rn(s1v, s1a[j]); s2v = __fadd2_rn(s2v, s2a[j]); }
+                const float inv_d = 1.0f / (float)D;
+                const float c1 = warp_sum(s1v.x + s1v.y) * inv_d, c2 = warp_sum(s2v.x + s2v.y) * inv_d;
                 const float2 nc1 = make_float2(-c1, -c1), nc2 = make_float2(-c2, -c2);
                 uint4* dxr = (uint4*)(dx + row * D);
 #pragma unroll

@@ -395,9 +395,19 @@ def run_ours(args):
     ms_e2e = max_over_ranks(e2.elapsed_time(e3)) / args.steps
     e2e_value = world * B / (ms_e2e / 1e3)
 
-    if rank != 0:
+    def finish():
+        """Leave the process group.  A captured graph holds NCCL kernels of this communicator: release it first, and do not let
+        a straggling communicator teardown hold the process after the result line is out."""
         if world > 1:
+            if use_graph:
+                torch.cuda.synchronize()
+                dist.barrier()
+                _REAL_STDOUT.flush()
+                os._exit(0)
             dist.destroy_process_group()
+
+    if rank != 0:
+        finish()
         return
 
     # ---------------- per-family device time and roofline ----------------
@@ -457,8 +467,7 @@ def run_ours(args):
             "step_tensor": {"algorithmic_tflops": step_tf, "peak": pk["tf_sust"], "frac": step_tf / pk["tf_sust"] if step_tf else None},
             "cpu_baseline": cpu_baseline}
     emit(line)
-    if world > 1:
-        dist.destroy_process_group()
+    finish()
 
 
 # =====================================================================================================================
