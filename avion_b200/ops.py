@@ -5,6 +5,7 @@ avion_b200/torch_ops.py), whose CUDA implementation is the ctypes call.  PyTorch
 operator dispatch.  Every function launches on torch's current CUDA stream.
 """
 import ctypes as C
+import os
 
 import torch
 
@@ -23,16 +24,21 @@ TIMED_BY_EPILOGUE = False      # True: one GEMM family per (mode, epilogue) = pe
 _EPI_NAMES = ("none", "bias", "bias_gelu", "bias_gelu_dual", "bias_residual", "dgelu", "f32_add")
 
 
+NVTX = os.environ.get("AVN_NVTX", "0") == "1"      # one NVTX range per kernel family call (nsys / ncu --nvtx filters)
+
+
 class _timed:
     def __init__(self, name, t, work=0.0):
         self.on = TIMED is not None
         self.work = work
+        self.name = name
         if self.on:
-            self.name = name
             self.s, self.e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             self.stream = torch.cuda.current_stream(t.device)
 
     def __enter__(self):
+        if NVTX:
+            torch.cuda.nvtx.range_push("avion_b200." + self.name)
         if self.on:
             self.s.record(self.stream)
 
@@ -40,6 +46,8 @@ class _timed:
         if self.on:
             self.e.record(self.stream)
             TIMED.setdefault(self.name, []).append((self.s, self.e, self.work))
+        if NVTX:
+            torch.cuda.nvtx.range_pop()
 
 
 def _cuda(t):
