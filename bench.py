@@ -357,7 +357,7 @@ def run_ours(args):
         timed, ops.TIMED = ops.TIMED, None
     ms_total = max_over_ranks(e0.elapsed_time(e1))
     clocks = sampler.stop() if rank == 0 else None
-    loss_val = float(out["loss"])
+    loss_val = float(out["loss"].detach())
     ms_step = ms_total / args.steps
     value = world * B / (ms_step / 1e3)
 
