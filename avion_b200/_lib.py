@@ -49,6 +49,8 @@ SIGNATURES = {
     "avn_head_bwd": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp],
     "avn_infonce_fwd": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp],
     "avn_infonce_bwd": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp, _f, _i, _vp, _vp, _vp, _vp],
+    "avn_infonce_static_max_floats": [],
+    "avn_infonce_bwd_static": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp, _f, _i, _vp, _vp, _vp],
     "avn_adamw_chunk_elems": [],
     "avn_adamw_step": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _f, _f, _f, _f, _i, _vp],
     "avn_clamp_scalar_f32": [_vp, _f, _f, _vp],
@@ -65,7 +67,7 @@ SIGNATURES = {
 }
 
 # kernels launched per C-ABI call (for the bench's gpu_launches count); default 1
-KERNELS_PER_CALL = {"avn_attn_bwd": 3, "avn_infonce_bwd": 3, "avn_head_bwd": 2, "avn_pos_table_bwd": 2,
+KERNELS_PER_CALL = {"avn_attn_bwd": 3, "avn_infonce_bwd": 3, "avn_infonce_bwd_static": 3, "avn_infonce_static_max_floats": 0, "avn_head_bwd": 2, "avn_pos_table_bwd": 2,
                     "avn_token_embed_bwd": 2, "avn_sample_rrc_boxes": 0, "avn_device_check": 0, "avn_version": 0,
                     "avn_adamw_chunk_elems": 0, "avn_mse_workspace_floats": 0, "avn_mse_fwd": 2,
                     "avn_mmr_workspace_floats": 0, "avn_mmr_fwd": 3}

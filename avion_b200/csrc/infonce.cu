@@ -6,9 +6,17 @@
 #include "common.cuh"
 #include "../../include/avion_b200.h"
 
+#include <mutex>
+
 namespace {
 using namespace avn;
 constexpr int ROWS = 8;
+
+// Scratch of avn_infonce_bwd_static: d(logit) [2][n][N] fp32 for callers that may not allocate (CUDA-graph capture, serving
+// loops).  4 MiB, held by every GPU that loads the library until the process exits.  In HOST code `g_static_dlogits` is only a
+// stand-in for the symbol: its device address comes from cudaGetSymbolAddress (static_dlogits_ptr below).
+constexpr long long STATIC_DLOGITS_FLOATS = 1ll << 20;
+static __device__ __align__(256) float g_static_dlogits[STATIC_DLOGITS_FLOATS];
 
 // Block = 8 local rows of one direction; thread t owns columns t, t+256, ...
 template <bool BWD>
@@ -178,4 +186,45 @@ extern "C" int avn_infonce_bwd(const float* img, const float* txt, const float* 
     infonce_drows_kernel<<<dim3((unsigned)((nr + 255) / 256), 2), 256, 0, stream>>>(all_img, all_txt, dlogits, d_all, n, N, E, row_offset);
     AVN_CHECK_CUDA(cudaGetLastError());
     return AVN_OK;
+}
+
+// ---- no-allocation variant ---------------------------------------------------------------------------------------------
+namespace {
+constexpr int MAX_DEVICES = 64;
+std::mutex g_static_mu;
+float* g_static_ptr[MAX_DEVICES] = {};
+
+// Device address of g_static_dlogits on the CURRENT device, resolved once per device.
+int static_dlogits_ptr(float** out) {
+    int dev = -1;
+    AVN_CHECK_CUDA(cudaGetDevice(&dev));
+    AVN_REQUIRE(dev >= 0 && dev < MAX_DEVICES, "infonce_bwd_static: device ordinal %d out of range", dev);
+    std::lock_guard<std::mutex> lock(g_static_mu);
+    if (!g_static_ptr[dev]) {
+        float* p = nullptr;
+        AVN_CHECK_CUDA(cudaGetSymbolAddress((void**)&p, g_static_dlogits));
+        AVN_REQUIRE(p != nullptr, "infonce_bwd_static: cudaGetSymbolAddress returned a null address");
+        g_static_ptr[dev] = p;
+    }
+    *out = g_static_ptr[dev];
+    return AVN_OK;
+}
+}  // namespace
+
+extern "C" int avn_infonce_static_max_floats(void) { return (int)STATIC_DLOGITS_FLOATS; }
+
+extern "C" int avn_infonce_bwd_static(const float* img, const float* txt, const float* all_img, const float* all_txt,
+                                      const float* scale, int n, int N, int E, int row_offset, const float* lse, float gscale,
+                                      int col_side, float* d_all, float* dscale, avn_stream_t stream) {
+    AVN_REQUIRE(n > 0 && N >= n, "infonce_bwd_static: bad sizes n=%d N=%d", n, N);
+    AVN_REQUIRE(2ll * n * N <= STATIC_DLOGITS_FLOATS,
+                "infonce_bwd_static: 2*n*N = %lld floats exceeds the static scratch of %lld floats (use avn_infonce_bwd with a "
+                "caller-provided workspace)", 2ll * n * N, STATIC_DLOGITS_FLOATS);
+    float* dlogits = nullptr;
+    const int rc = static_dlogits_ptr(&dlogits);
+    if (rc != AVN_OK) return rc;
+    // every element [dir][r < n][j < N] of the scratch is written by the rows kernel before the dcols / drows kernels read
+    // it (same stream), so the previous call's contents need no clearing
+    return avn_infonce_bwd(img, txt, all_img, all_txt, scale, n, N, E, row_offset, lse, gscale, col_side, dlogits, d_all, dscale,
+                           stream);
 }

@@ -55,6 +55,8 @@ KERNELS = {
                    "Tensor(a!) lse, Tensor(b!) out",
     "infonce_bwd": "Tensor img, Tensor txt, Tensor all_img, Tensor all_txt, Tensor scale, int n, int N, int E, int row_offset, "
                    "Tensor lse, float gscale, bool col_side, Tensor(a!) dlogits, Tensor(b!) d_all, Tensor(c!) dscale",
+    "infonce_bwd_static": "Tensor img, Tensor txt, Tensor all_img, Tensor all_txt, Tensor scale, int n, int N, int E, "
+                          "int row_offset, Tensor lse, float gscale, bool col_side, Tensor(a!) d_all, Tensor(b!) dscale",
     "adamw_step": "Tensor params, Tensor grads, Tensor exp_avg, Tensor exp_avg_sq, Tensor sizes, Tensor wd, Tensor chunk_tensor, "
                   "Tensor chunk_offset, int n_chunks, float lr, float beta1, float beta2, float eps, int step",
     "clamp_scalar_f32": "Tensor(a!) x, float lo, float hi",

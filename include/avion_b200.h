@@ -149,6 +149,18 @@ int avn_infonce_fwd(const float* img, const float* txt, const float* all_img, co
 int avn_infonce_bwd(const float* img, const float* txt, const float* all_img, const float* all_txt, const float* scale,
                     int n, int N, int E, int row_offset, const float* lse, float gscale, int col_side, float* dlogits,
                     float* d_all, float* dscale, avn_stream_t stream);
+/* No counterpart in the reference: added for callers that cannot allocate device
+ * memory (code under CUDA-graph capture, tight serving loops, harnesses that forbid cudaMalloc).  Same computation and
+ * arguments as avn_infonce_bwd minus the dlogits workspace, which lives in a file-scope `static __device__` array of
+ * avn_infonce_static_max_floats() = 2^20 floats (4 MiB per GPU that loads the library, held until exit).  Requires
+ * 2*n*N <= that maximum (e.g. n = 256 local rows x N = 2048 gathered rows), otherwise returns AVN_ERR_ARG with a message.
+ * Allocates nothing (no cudaMalloc / cudaFree / library allocation); the first call on each device resolves the array's
+ * address with cudaGetSymbolAddress.  The scratch is fully rewritten by every call (nothing to clear), but it is SHARED: two
+ * calls that overlap on one GPU (different streams, or concurrent graph branches) race - serialise them. */
+int avn_infonce_static_max_floats(void);
+int avn_infonce_bwd_static(const float* img, const float* txt, const float* all_img, const float* all_txt, const float* scale,
+                           int n, int N, int E, int row_offset, const float* lse, float gscale, int col_side, float* d_all,
+                           float* dscale, avn_stream_t stream);
 
 /* ---- O1: optimizer step (scripts/main_lavila_pretrain.py:296-341 AdamW with weight-decay / no-decay groups; :880 clamp) --
  * One launch updates every tensor: device tables of n tensors (params, grads, exp_avg, exp_avg_sq: fp32 pointers; sizes in
