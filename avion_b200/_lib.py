@@ -22,7 +22,7 @@ class GemmDesc(C.Structure):
                 ("C", _vp), ("ldc", _i64), ("c_batch_stride", _i64),
                 ("C2", _vp), ("bias", _vp),
                 ("R", _vp), ("ldr", _i64), ("r_batch_stride", _i64),
-                ("splits", _i)]
+                ("splits", _i), ("colsum", _vp)]
 
 
 # name -> argtypes; every function returns int (0 = ok) unless noted

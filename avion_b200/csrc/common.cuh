@@ -238,6 +238,35 @@ __device__ __forceinline__ void mbar_arrive_leader(uint64_t* bar) {
 #endif
 }
 
+// arrive on the copy of a barrier that lives in CTA `rank` of the cluster.  Relaxed (a .release.cluster arrive is a
+// cluster-scope memory barrier: issued once per k-block it more than doubled the weight-gradient GEMM's time); used to forward
+// "the TMA data of this stage has landed", which the async proxy has already made visible in the destination CTA.
+__device__ __forceinline__ void mbar_arrive_rank(uint64_t* bar, uint32_t rank) {
+    uint32_t remote;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(smem_u32(bar)), "r"(rank));
+#ifdef AVN_ARRIVE_RELEASE
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(remote) : "memory");
+#else
+    asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(remote) : "memory");
+#endif
+}
+__device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity) {
+    uint32_t addr = smem_u32(bar), done = 0;
+    for (uint32_t spin = 0; !done; ++spin) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(addr), "r"(parity)
+            : "memory");
+        if (!done && spin > (1u << AVN_SPIN_LOG2)) {
+            printf("avion_b200: cluster mbarrier timeout block %d thread %d bar %u parity %u\n", blockIdx.x, threadIdx.x, addr, parity);
+            __trap();
+        }
+    }
+}
+
 // Instruction descriptor: bf16 x bf16 -> fp32, M x N tile (cute::UMMA::InstrDescriptor bit layout).
 __host__ __device__ constexpr uint32_t umma_idesc_bf16(int M, int N, bool a_mn_major, bool b_mn_major) {
     return (1u << 4) | (1u << 7) | (1u << 10) | ((a_mn_major ? 1u : 0u) << 15) | ((b_mn_major ? 1u : 0u) << 16) |

@@ -7,6 +7,10 @@
 //   NT: A K-major, B K-major        (forward:  X[M,K] * W[N,K]^T)
 //   NN: A K-major, B MN-major       (dgrad:    dY[M,N'] * W[N',K'])
 //   TN: A MN-major, B MN-major      (wgrad:    dY[tok,N]^T * X[tok,K], contraction over tokens, split-K)
+// TN can also produce the bias gradient (column sums of dY over the tokens) from the A tiles it stages anyway: the epilogue
+// warps, idle during the main loop of a weight-gradient tile, read A stages while the MMAs consume them and add them into
+// per-thread fp32 sums; a stage returns to the producer when the MMA commit AND epilogue warp 0 have arrived (no second pass
+// over dY in HBM, nothing added to the latency of a stage's release).
 // Replaces the cuBLAS calls behind nn.Linear / FlashMHA / FlashMlp in avion/models/transformer.py:116-120,135,227,320.
 #include <stdlib.h>
 #include "common.cuh"
@@ -17,6 +21,7 @@ using namespace avn;
 
 constexpr int BM = 128, BK = 64;
 constexpr int EPI_WARPS = 8;
+
 constexpr int NTHREADS = 64 + EPI_WARPS * 32;
 constexpr int A_STAGE_BYTES = BM * BK * 2;       // 16 KB
 constexpr int STG_BYTES = 128 * 128;             // one 128-row x 128-byte staging tile per epilogue group
@@ -27,6 +32,7 @@ struct KParams {
     const float* bias;
     const __nv_bfloat16* R;
     long long ldr, r_batch_stride;
+    float* colsum;      // TN only: fp32 [M] += column sums of A over the contraction, or nullptr
 };
 
 // CG = CTAs per MMA (cta_group): with CG = 2 a CTA pair computes a 256 x BN tile, each CTA staging its own 128 rows of A and
@@ -62,7 +68,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     uint64_t* empty_bar = full_bar + STAGES;
     uint64_t* tfull_bar = empty_bar + STAGES;
     uint64_t* tempty_bar = tfull_bar + 2;
-    uint32_t* tmem_ptr = (uint32_t*)(tempty_bar + 2);
+    uint64_t* pfull_bar = tempty_bar + 2;       // column-sum mode, peer CTA of a pair: "stage is full", forwarded by the leader
+    uint32_t* tmem_ptr = (uint32_t*)(pfull_bar + STAGES);
+    const bool colsum_on = (MODE == AVN_GEMM_TN) && p.colsum != nullptr;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int rank = (CG == 2) ? (int)cluster_ctarank() : 0;      // position inside the CTA pair; rank 0 issues the MMAs
@@ -71,7 +79,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         tma_prefetch_desc(&tmA);
         tma_prefetch_desc(&tmB);
         tma_prefetch_desc(&tmC);
-        for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
+        // column-sum mode: a stage is released by the MMA commit plus the arrive of epilogue warp 0
+        for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], colsum_on ? 2 : 1); mbar_init(&pfull_bar[i], 1); }
         for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], EPI_WARPS * CG); }
         fence_barrier_init();
     }
@@ -178,12 +187,75 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         float* bias_s = sBias + g * (BN / 2);
         constexpr int UNITS = BN / 2 / 32;      // 32-column units per group
         int acc = 0; uint32_t acc_phase = 0;
+        int cs_stage = 0; uint32_t cs_phase = 0;
         for (int t = tile0; t < total_tiles; t += tile_step) {
             int n_blk = t % p.n_tiles; int r = t / p.n_tiles;
             int m_blk = (r % m_units) * CG + rank; int outer = r / m_units;
             const int mb = (MODE == AVN_GEMM_TN) ? 0 : outer;
             const int m0 = m_blk * BM, n0 = n_blk * BN + g * (BN / 2);
             const int m = m0 + row;
+            if (MODE == AVN_GEMM_TN && colsum_on) {
+                // ---- bias gradient: column sums of this CTA's 128 columns of A over the contraction ----
+                // The n_tiles tiles of a row of tiles stage the same A panel: each sums the k-blocks kb = n_blk (mod n_tiles), so
+                // the extra shared-memory reads (they compete with the tensor core's operand fetch: one tile reading every
+                // stage ran 17 % longer) are spread over all CTAs.  Epilogue warp 0 walks the ring - it waits for a stage to
+                // land and is the one extra arrival a stage's release counts in this mode; on a k-block of this tile all
+                // eight warps read the stage (thread = 16-byte chunk of 8 columns x 4 of the 64 k-rows) before it arrives.
+                const int et = threadIdx.x - 64, mc = et & 15, kg = et >> 4;
+                const uint32_t a_off = (uint32_t)((mc >> 3) * 8192 + kg * 4 * 128);
+                float2 cs[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) cs[i] = make_float2(0.f, 0.f);
+                const int kb0 = outer * p.kb_per_split, kb1 = min(p.total_kb, kb0 + p.kb_per_split);
+                int next_mine = kb0 + n_blk;
+                for (int kb = kb0; kb < kb1; ++kb) {
+                    const bool mine = (kb == next_mine);
+                    if (mine) next_mine += p.n_tiles;
+                    if (ew == 0) {
+                        if (CG == 2 && rank == 1) {
+                            mbar_wait(&pfull_bar[cs_stage], cs_phase);
+                        } else {
+                            mbar_wait(&full_bar[cs_stage], cs_phase);    // the stage has landed; it is not refilled before we arrive
+                            // the peer's full barrier is never signalled (its loads count on this one): tell its warp 0
+                            if (CG == 2 && lane == 0) mbar_arrive_rank(&pfull_bar[cs_stage], 1);
+                        }
+                    }
+                    if (mine) {
+                        named_bar_sync(3, EPI_WARPS * 32);               // warp 0 has seen the stage
+                        const uint32_t a = smem_u32(sA + cs_stage * A_STAGE_BYTES) + a_off;
+#pragma unroll
+                        for (int rr = 0; rr < 4; ++rr) {
+                            const int k7 = (kg * 4 + rr) & 7;
+                            uint4 v;
+                            asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                                         : "r"(a + rr * 128 + (((mc & 7) ^ k7) << 4)));
+                            cs[0] = __fadd2_rn(cs[0], unpack_bf16(v.x)); cs[1] = __fadd2_rn(cs[1], unpack_bf16(v.y));
+                            cs[2] = __fadd2_rn(cs[2], unpack_bf16(v.z)); cs[3] = __fadd2_rn(cs[3], unpack_bf16(v.w));
+                        }
+                        // the loads above have returned (their values were consumed): warps 1-7 check in, warp 0 collects
+                        if (ew == 0) named_bar_sync(4, EPI_WARPS * 32); else named_bar_arrive(4, EPI_WARPS * 32);
+                    }
+                    if (ew == 0) {
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(&empty_bar[cs_stage]);
+                    }
+                    if (++cs_stage == STAGES) { cs_stage = 0; cs_phase ^= 1; }
+                }
+                // 16 k-groups -> one sum per column: through the (idle) staging tiles, then one atomic per column
+                if (gtid == 0) tma_wait_group_read0();               // a previous tile's reduce-add may still read the staging tiles
+                named_bar_sync(3, EPI_WARPS * 32);
+                float* red = (float*)sStg;                           // [16 k-groups][128 columns]
+                *(float4*)(red + kg * 128 + mc * 8) = make_float4(cs[0].x, cs[0].y, cs[1].x, cs[1].y);
+                *(float4*)(red + kg * 128 + mc * 8 + 4) = make_float4(cs[2].x, cs[2].y, cs[3].x, cs[3].y);
+                named_bar_sync(3, EPI_WARPS * 32);
+                if (et < BM && m0 + et < p.M) {
+                    float tot = 0.f;
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) tot += red[i * 128 + et];
+                    atomicAdd(p.colsum + m0 + et, tot);
+                }
+                named_bar_sync(3, EPI_WARPS * 32);                   // the epilogue below reuses the staging tiles
+            }
             if (EPI == AVN_EPI_BIAS || EPI == AVN_EPI_BIAS_GELU || EPI == AVN_EPI_BIAS_GELU_DUAL || EPI == AVN_EPI_BIAS_RESIDUAL) {
                 named_bar_sync(bar_id, 128);    // previous tile's readers of bias_s are done
                 if (gtid < BN / 2) bias_s[gtid] = (p.bias != nullptr && n0 + gtid < p.N) ? p.bias[n0 + gtid] : 0.f;
@@ -392,6 +464,7 @@ int launch(const avn_gemm_desc* d, cudaStream_t stream) {
     p.splits = (p.total_kb + p.kb_per_split - 1) / p.kb_per_split;
     p.bias = d->bias;
     p.R = (const __nv_bfloat16*)d->R; p.ldr = d->ldr; p.r_batch_stride = d->r_batch_stride;
+    p.colsum = tn ? d->colsum : nullptr;
     const int total_tiles = (tn ? p.splits : d->batch) * ((p.m_tiles + CG - 1) / CG) * p.n_tiles;
     int grid = avn_num_sms() / CG;          // CTA pairs (or CTAs)
     if (grid > total_tiles) grid = total_tiles;

@@ -18,6 +18,7 @@ from .. import ops
 from ..ops import (EPI_BIAS, EPI_BIAS_GELU, EPI_BIAS_GELU_DUAL, EPI_BIAS_RESIDUAL, EPI_DGELU, EPI_F32_ADD, EPI_NONE, GEMM_NT,
                    GEMM_TN, bf16, f32)
 
+FOLD_BIAS_GRAD = os.environ.get("AVN_FOLD_BIAS_GRAD", "1") != "0"      # "0": separate column-sum launches (A/B runs)
 BLOCK_KEYS = ("ln1_w", "ln1_b", "qkv_w", "qkv_b", "out_w", "out_b", "ln2_w", "ln2_b", "fc1_w", "fc1_b", "fc2_w", "fc2_b")
 _MATS = ("qkv_w", "out_w", "fc1_w", "fc2_w")
 
@@ -108,12 +109,15 @@ def blocks_backward(g, saved, layers, grads, heads, eps, causal, ws, last_colsum
         a = ws.get("a", (B, S, Hd), bf16, dev)
         pre = ws.get("pre", (B, S, Hd), bf16, dev)      # receives gelu'(fc1 pre-activation)
         ops.linear_fwd(h, L["fc1_w"], L["fc1_b"], EPI_BIAS_GELU_DUAL, out=a, out2=pre)
-        if not fc2_bias_done:
+        # bias gradients = column sums of the incoming gradient: taken by the weight-gradient GEMM from the tiles it stages
+        # anyway (FOLD_BIAS_GRAD; the two that feed a residual stream come out of the LayerNorm backward)
+        if not fc2_bias_done and not FOLD_BIAS_GRAD:
             ops.colsum(g, G["fc2_b"])
-        ops.linear_wgrad(g, a, G["fc2_w"])
+        ops.linear_wgrad(g, a, G["fc2_w"], dbias=G["fc2_b"] if (FOLD_BIAS_GRAD and not fc2_bias_done) else None)
         dpre = ops.linear_dgrad(g, L["fc2_w"], EPI_DGELU, pre=pre, out=a)      # a is dead after the wgrad: reuse it
-        ops.colsum(dpre, G["fc1_b"])
-        ops.linear_wgrad(dpre, h, G["fc1_w"])
+        if not FOLD_BIAS_GRAD:
+            ops.colsum(dpre, G["fc1_b"])
+        ops.linear_wgrad(dpre, h, G["fc1_w"], dbias=G["fc1_b"] if FOLD_BIAS_GRAD else None)
         dh = ops.linear_dgrad(dpre, L["fc1_w"], out=ws.get("dh", (B, S, D), bf16, dev))
         g1 = ws.get("g1", (B, S, D), bf16, dev)
         ops.layernorm_bwd(dh, x_mid, L["ln2_w"], m2, r2, G["ln2_w"], G["ln2_b"], dres=g, dcolsum=G["out_b"], out=g1)
@@ -123,14 +127,15 @@ def blocks_backward(g, saved, layers, grads, heads, eps, causal, ws, last_colsum
         dqkv = ops.attn_bwd(qkv, o, do, lse, heads, scale, causal, dqkv=ws.get("dqkv", (B, S, 3 * D), bf16, dev),
                             dq_acc=ws.get("dq_acc", (B, S, D), f32, dev))
         del qkv, o, lse
-        ops.colsum(dqkv, G["qkv_b"])
+        if not FOLD_BIAS_GRAD:
+            ops.colsum(dqkv, G["qkv_b"])
         del h, h2
         if h1 is not None:
             h = h1
         else:
             h = ws.get("h", (B, S, D), bf16, dev)
             ops.layernorm_fwd(x_in, L["ln1_w"], L["ln1_b"], eps, out=h, save_stats=False)
-        ops.linear_wgrad(dqkv, h, G["qkv_w"])
+        ops.linear_wgrad(dqkv, h, G["qkv_w"], dbias=G["qkv_b"] if FOLD_BIAS_GRAD else None)
         dh1 = ops.linear_dgrad(dqkv, L["qkv_w"], out=dh)
         # dL/dx_in = g1 + LN1'(dh1); its column sum is the fc2 bias gradient of the block below
         below = grads[li - 1]["fc2_b"] if li > 0 else None

@@ -37,8 +37,7 @@ class _DenseFn(torch.autograd.Function):
         dyb[:, :N] = dy
         dw = torch.zeros(Np, K, dtype=torch.float32, device=xb.device)
         db = torch.zeros(Np, dtype=torch.float32, device=xb.device)
-        ops.linear_wgrad(dyb, xb, dw)
-        ops.colsum(dyb, db)
+        ops.linear_wgrad(dyb, xb, dw, dbias=db)          # bias gradient from the dy tiles the GEMM stages
         dx = ops.linear_dgrad(dyb, wb)
         return dx.to(xdtype), dw[:N], db[:N]
 

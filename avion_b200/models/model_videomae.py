@@ -174,9 +174,8 @@ class _VideoMAEFn(torch.autograd.Function):
         (g_pe_w, g_pe_b, g_encn_w, g_encn_b, g_e2d, g_mask, g_decn_w, g_decn_b, g_head_w, g_head_b) = E.zeros_f32_like_many(
             [pe_w, pe_b, encn_w, encn_b, e2d_w, mask_token, decn_w, decn_b, head_w, head_b])
         # ---- head
-        ops.colsum(dout, g_head_b)
         ops.gemm(GEMM_TN, EPI_F32_ADD, Fo, Dd, Nm, dout, Fo, yn[:, Nv:], Dd, g_head_w, Dd, batch=B, a_bs=Nm * Fo, b_bs=N * Dd,
-                 splits=0)
+                 splits=0, colsum=g_head_b)           # + the head's bias gradient, from the dout tiles the GEMM stages
         dyn = ws_d.get("dh", (B, N, Dd), bf16, dev)
         dyn.zero_()                                   # the visible rows of the decoder output receive no gradient
         ops.gemm(GEMM_NN, EPI_NONE, Nm, Dd, Fo, dout, Fo, head_bf, Dd, dyn[:, Nv:], Dd, batch=B, a_bs=Nm * Fo, c_bs=N * Dd)
@@ -193,8 +192,7 @@ class _VideoMAEFn(torch.autograd.Function):
         del dx_full, dxn, x_enc, xn
         # ---- encoder blocks, patch embedding (the position table is a constant)
         dx0 = E.blocks_backward(g, ctx.saved_e, layers[:n_enc], grads[:n_enc], enc_heads, eps, False, ws_e)
-        ops.colsum(dx0, g_pe_b)
-        ops.linear_wgrad(dx0, patches, g_pe_w)
+        ops.linear_wgrad(dx0, patches, g_pe_w, dbias=g_pe_b)
         ctx.saved_e = ctx.saved_d = ctx.layers = ctx.misc = None
         flat_grads = [G_[k] for G_ in grads for k in E.BLOCK_KEYS]
         return (None, None, None, g_pe_w, g_pe_b, g_encn_w, g_encn_b, g_e2d, g_mask, g_decn_w, g_decn_b, g_head_w, g_head_b,

@@ -141,13 +141,13 @@ def layernorm_bwd(dy, x, gamma, mean, rstd, dgamma, dbeta, dres=None, dcolsum=No
 
 
 def gemm(mode, epi, M, N, Kd, A, lda, B, ldb, Cm, ldc, batch=1, a_bs=0, b_bs=0, c_bs=0, C2=None, bias=None, R=None, ldr=0,
-         r_bs=0, splits=1):
+         r_bs=0, splits=1, colsum=None):
     """Raw descriptor-level GEMM (see include/avion_b200.h); A/B/Cm/C2/R are tensors whose data_ptr is the origin."""
     name = "gemm_%s" % ("nt", "nn", "tn")[mode]
     if TIMED_BY_EPILOGUE:
         name += "_" + _EPI_NAMES[epi]
     with _timed(name, _cuda(A), 2.0 * M * N * Kd * batch):
-        K.gemm_bf16(mode, epi, M, N, Kd, batch, A, lda, a_bs, B, ldb, b_bs, Cm, ldc, c_bs, C2, bias, R, ldr, r_bs, splits)
+        K.gemm_bf16(mode, epi, M, N, Kd, batch, A, lda, a_bs, B, ldb, b_bs, Cm, ldc, c_bs, C2, bias, R, ldr, r_bs, splits, colsum)
 
 
 def linear_fwd(x, w, bias=None, epi=EPI_NONE, residual=None, out=None, out2=None):
@@ -174,12 +174,16 @@ def linear_dgrad(dy, w, epi=EPI_NONE, pre=None, out=None):
     return dx
 
 
-def linear_wgrad(dy, x, dw):
-    """dw[N,K] (fp32) += dy[tok,N]^T @ x[tok,K]."""
+def linear_wgrad(dy, x, dw, dbias=None):
+    """dw[N,K] (fp32) += dy[tok,N]^T @ x[tok,K]; with dbias (fp32 [N]): dbias += dy.sum over the tokens, from the dy tiles the
+    GEMM stages anyway (no separate pass over dy)."""
     _chk(dy, bf16, "dy"); _chk(x, bf16, "x"); _chk(dw, f32, "dw")
     N, K = dw.shape
     tok = dy.numel() // N
-    gemm(GEMM_TN, EPI_F32_ADD, N, K, tok, dy, N, x, K, dw, K, splits=0)      # 0: the library picks the split-K count
+    if dbias is not None:
+        _chk(dbias, f32, "dbias")
+        assert dbias.numel() == N
+    gemm(GEMM_TN, EPI_F32_ADD, N, K, tok, dy, N, x, K, dw, K, splits=0, colsum=dbias)      # 0: the library picks the split-K count
     return dw
 
 

@@ -71,7 +71,8 @@ KERNELS = {
     "mmr_bwd": "Tensor ws, Tensor gloss, int n, int E, float margin, bool fix_norm, Tensor(a!) dtext, Tensor(b!) dimage",
 }
 GEMM_SCHEMA = ("int mode, int epi, int M, int N, int K, int batch, Tensor A, int lda, int a_bs, Tensor B, int ldb, int b_bs, "
-               "Tensor(a!) C, int ldc, int c_bs, Tensor(b!)? C2, Tensor? bias, Tensor? R, int ldr, int r_bs, int splits")
+               "Tensor(a!) C, int ldc, int c_bs, Tensor(b!)? C2, Tensor? bias, Tensor? R, int ldr, int r_bs, int splits, "
+               "Tensor(c!)? colsum=None")
 
 
 def _stream_of(t):
@@ -115,10 +116,11 @@ def _noop(*args):
     return None
 
 
-def _gemm_impl(mode, epi, M, N, K, batch, A, lda, a_bs, B, ldb, b_bs, Cm, ldc, c_bs, C2, bias, R, ldr, r_bs, splits):
+def _gemm_impl(mode, epi, M, N, K, batch, A, lda, a_bs, B, ldb, b_bs, Cm, ldc, c_bs, C2, bias, R, ldr, r_bs, splits, colsum=None):
     d = _lib.GemmDesc(mode, epi, M, N, K, batch, A.data_ptr(), lda, a_bs, B.data_ptr(), ldb, b_bs, Cm.data_ptr(), ldc, c_bs,
                       C2.data_ptr() if C2 is not None else None, bias.data_ptr() if bias is not None else None,
-                      R.data_ptr() if R is not None else None, ldr, r_bs, splits)
+                      R.data_ptr() if R is not None else None, ldr, r_bs, splits,
+                      colsum.data_ptr() if colsum is not None else None)
     _lib.call("avn_gemm_bf16", C.byref(d), _stream_of(A))
 
 

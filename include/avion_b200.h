@@ -87,6 +87,9 @@ typedef struct {
     const float* bias;                             /* fp32 [N] */
     const void* R; int64_t ldr, r_batch_stride;    /* bf16, indexed like C */
     int splits;                                    /* TN only: split of the contraction across CTAs; 0 = chosen by the library */
+    float* colsum;                                 /* TN only, may be NULL: fp32 [M], colsum[m] += sum_b sum_k A[b][k][m] - the bias
+                                                      gradient of the Linear whose weight gradient this call computes (the
+                                                      `.sum(0)` autograd runs on dY), taken from the A tiles the kernel stages anyway */
 } avn_gemm_desc;
 int avn_gemm_bf16(const avn_gemm_desc* d, avn_stream_t stream);
 

@@ -185,6 +185,25 @@ def test_gemm_tn_wgrad(ops, tok, N, K):
     assert rel_err(dw, 1 + dy.float().T @ x.float()) < 3e-3
 
 
+@pytest.mark.parametrize("tok,N,K", [(4096, 768, 768), (3137 * 4, 2304, 768), (8200, 3072, 768), (1000, 512, 2048), (520, 200, 96),
+                                     (77 * 16, 1536, 512), (64, 256, 256), (200000, 256, 256)])
+def test_gemm_tn_wgrad_with_bias_gradient(ops, tok, N, K):
+    """The weight-gradient GEMM also returns dY.sum(0) (the bias gradient) from the dY tiles it stages: every tile geometry
+    (CTA pairs / single CTA, 256- and 128-wide, ragged M and token counts, several tiles per CTA, split-K), accumulating."""
+    dy, x = rnd(tok, N, seed=17), rnd(tok, K, seed=18)
+    dw = torch.ones(N, K, device="cuda")
+    db = torch.full((N,), 2.0, device="cuda")
+    ops.linear_wgrad(dy, x, dw, dbias=db)
+    assert rel_err(dw, 1 + dy.float().T @ x.float()) < 3e-3
+    ref = 2 + dy.float().sum(0)
+    assert rel_err(db, ref) < 5e-5, rel_err(db, ref)
+    ops.linear_wgrad(dy, x, dw, dbias=db)                 # += on both outputs
+    assert rel_err(db, 2 + 2 * dy.float().sum(0)) < 5e-5
+    dw2 = torch.ones(N, K, device="cuda")
+    ops.linear_wgrad(dy, x, dw2)                          # without the bias gradient: same weight gradient path as before
+    assert rel_err(dw2, 1 + dy.float().T @ x.float()) < 3e-3
+
+
 def test_gemm_batched_patch_embed_layout(ops):
     """Patch-embed geometry: A [B][P][K] -> C rows 1.. of [B][P+1][D] with a shared residual table."""
     B, P, K, D = 3, 196, 256, 384

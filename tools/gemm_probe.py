@@ -1,7 +1,8 @@
 #!/usr/bin/env python
 """Time / profile one GEMM shape of the train step in isolation: python tools/gemm_probe.py MODE M N K [reps]
 MODE = nt | nn | tn; shapes in the C = A x B convention of avn_gemm_bf16 (tn: C[M,N] += A[K,M]^T B[K,N], fp32).
-Environment: AVN_GEMM_CG=1 forces single-CTA tiles, AVN_GEMM_SPLITS=n forces the split-K count (tn)."""
+Environment: AVN_GEMM_CG=1 forces single-CTA tiles, AVN_GEMM_SPLITS=n forces the split-K count (tn), AVN_GEMM_COLSUM=1 also
+asks the tn kernel for the column sums of A (the bias gradient), =2 times a separate colsum launch after the GEMM instead."""
 import os
 import sys
 
@@ -19,7 +20,15 @@ if mode == "tn":
     a = (torch.randn(K, M, device="cuda") * 0.1).to(bf)
     b = (torch.randn(K, N, device="cuda") * 0.1).to(bf)
     c = torch.zeros(M, N, device="cuda")
-    fn = lambda: ops.gemm(ops.GEMM_TN, ops.EPI_F32_ADD, M, N, K, a, M, b, N, c, N, splits=splits)      # noqa: E731
+    cs_mode = int(os.environ.get("AVN_GEMM_COLSUM", "0"))
+    cs = torch.zeros(M, device="cuda")
+    if cs_mode == 2:
+        def fn():
+            ops.gemm(ops.GEMM_TN, ops.EPI_F32_ADD, M, N, K, a, M, b, N, c, N, splits=splits)
+            ops.colsum(a, cs)
+    else:
+        fn = lambda: ops.gemm(ops.GEMM_TN, ops.EPI_F32_ADD, M, N, K, a, M, b, N, c, N, splits=splits,      # noqa: E731
+                              colsum=cs if cs_mode == 1 else None)
 elif mode == "nt":
     a = (torch.randn(M, K, device="cuda") * 0.1).to(bf)
     b = (torch.randn(N, K, device="cuda") * 0.1).to(bf)
@@ -38,5 +47,6 @@ best = 1e9
 for _ in range(reps):
     e0.record(); fn(); e1.record(); torch.cuda.synchronize()
     best = min(best, e0.elapsed_time(e1))
-print(f"gemm {mode} M={M} N={N} K={K} cg={os.environ.get('AVN_GEMM_CG', 'auto')} splits={splits or 'auto'}: {best:.3f} ms  "
+print(f"gemm {mode} M={M} N={N} K={K} cg={os.environ.get('AVN_GEMM_CG', 'auto')} splits={splits or 'auto'} "
+      f"colsum={os.environ.get('AVN_GEMM_COLSUM', '0')}: {best:.3f} ms  "
       f"{2.0 * M * N * K / best / 1e9:.0f} TFLOP/s", flush=True)
