@@ -33,6 +33,7 @@ struct KParams {
     const __nv_bfloat16* R;
     long long ldr, r_batch_stride;
     float* colsum;      // TN only: fp32 [M] += column sums of A over the contraction, or nullptr
+    int a_box4, b_box4; // MN-major operand staged by ONE 4-D box per stage (64-column chunks as the third dimension)
 };
 
 // CG = CTAs per MMA (cta_group): with CG = 2 a CTA pair computes a 256 x BN tile, each CTA staging its own 128 rows of A and
@@ -108,6 +109,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                 auto load = [&](void* dst, const CUtensorMap* tm, uint64_t* bar, int c0, int c1, int c2) {
                     if (CG == 2) tma_load_3d_2cta(dst, tm, bar, c0, c1, c2); else tma_load_3d(dst, tm, bar, c0, c1, c2);
                 };
+                // MN-major operand: [k rows][64 columns] chunks; the 4-D map views the row as (chunk, 64 columns), so that one
+                // box brings all chunks of a stage ([chunk][k][128 B] in shared memory, as the per-chunk loads lay it out)
+                auto load4 = [&](void* dst, const CUtensorMap* tm, uint64_t* bar, int col0, int krow, int kbatch) {
+                    if (CG == 2) tma_load_4d_2cta(dst, tm, bar, 0, krow, col0 >> 6, kbatch); else tma_load_4d(dst, tm, bar, 0, krow, col0 >> 6, kbatch);
+                };
                 for (int kb = kb0; kb < kb1; ++kb) {
                     mbar_wait(&empty_bar[stage], phase ^ 1);
                     uint8_t* a = sA + stage * A_STAGE_BYTES;
@@ -116,14 +122,22 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                     if (rank == 0) mbar_expect_tx(&full_bar[stage], CG * (A_STAGE_BYTES + L::B_STAGE_BYTES));
                     if (MODE == AVN_GEMM_TN) {
                         int kbatch = kb / p.kblocks, krow = (kb % p.kblocks) * BK;
+                        if (p.a_box4) load4(a, &tmA, &full_bar[stage], m0, krow, kbatch);
+                        else {
 #pragma unroll
-                        for (int j = 0; j < BM / 64; ++j) load(a + j * 8192, &tmA, &full_bar[stage], m0 + 64 * j, krow, kbatch);
+                            for (int j = 0; j < BM / 64; ++j) load(a + j * 8192, &tmA, &full_bar[stage], m0 + 64 * j, krow, kbatch);
+                        }
+                        if (p.b_box4) load4(b, &tmB, &full_bar[stage], n0, krow, kbatch);
+                        else {
 #pragma unroll
-                        for (int j = 0; j < BN / CG / 64; ++j) load(b + j * 8192, &tmB, &full_bar[stage], n0 + 64 * j, krow, kbatch);
+                            for (int j = 0; j < BN / CG / 64; ++j) load(b + j * 8192, &tmB, &full_bar[stage], n0 + 64 * j, krow, kbatch);
+                        }
                     } else {
                         load(a, &tmA, &full_bar[stage], kb * BK, m0, outer);
                         if (MODE == AVN_GEMM_NT) {
                             load(b, &tmB, &full_bar[stage], kb * BK, n0, 0);
+                        } else if (p.b_box4) {
+                            load4(b, &tmB, &full_bar[stage], n0, kb * BK, 0);
                         } else {
 #pragma unroll
                             for (int j = 0; j < BN / CG / 64; ++j) load(b + j * 8192, &tmB, &full_bar[stage], n0 + 64 * j, kb * BK, 0);
@@ -395,6 +409,11 @@ int launch(const avn_gemm_desc* d, cudaStream_t stream) {
     CUtensorMap tmA, tmB, tmC, tmC2;
     const bool tn = (MODE == AVN_GEMM_TN);
     int rc;
+    // one 4-D box per MN-major operand and stage instead of one 3-D box per 64-column chunk (fewer TMA operations for the one
+    // producer thread).  Needs whole chunks (the view would wrap a ragged row into the next one); AVN_GEMM_BOX4=0 disables it.
+    static const bool box4_on = !(getenv("AVN_GEMM_BOX4") && atoi(getenv("AVN_GEMM_BOX4")) == 0);
+    auto box4_ok = [&](int cols) { return box4_on && cols % 64 == 0; };
+    bool a_box4 = false, b_box4 = false;
     // ---- A
     if (!tn) {
         uint64_t dims[3] = {(uint64_t)d->K, (uint64_t)d->M, (uint64_t)d->batch};
@@ -402,10 +421,19 @@ int launch(const avn_gemm_desc* d, cudaStream_t stream) {
         uint32_t box[3] = {64, 128, 1};
         if ((rc = avn_make_tmap(&tmA, d->A, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, 3, dims, str, box, true))) return rc;
     } else {
-        uint64_t dims[3] = {(uint64_t)d->M, (uint64_t)d->K, (uint64_t)d->batch};
-        uint64_t str[2] = {(uint64_t)d->lda * 2, (uint64_t)(d->batch > 1 ? d->a_batch_stride : d->lda * (int64_t)d->K) * 2};
-        uint32_t box[3] = {64, 64, 1};
-        if ((rc = avn_make_tmap(&tmA, d->A, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, 3, dims, str, box, true))) return rc;
+        const uint64_t bstr = (uint64_t)(d->batch > 1 ? d->a_batch_stride : d->lda * (int64_t)d->K) * 2;
+        if (box4_ok(d->M)) {
+            uint64_t dims[4] = {64, (uint64_t)d->K, (uint64_t)d->M / 64, (uint64_t)d->batch};
+            uint64_t str[3] = {(uint64_t)d->lda * 2, 128, bstr};
+            uint32_t box[4] = {64, 64, BM / 64, 1};
+            a_box4 = avn_make_tmap(&tmA, d->A, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, 4, dims, str, box, true) == AVN_OK;
+        }
+        if (!a_box4) {
+            uint64_t dims[3] = {(uint64_t)d->M, (uint64_t)d->K, (uint64_t)d->batch};
+            uint64_t str[2] = {(uint64_t)d->lda * 2, bstr};
+            uint32_t box[3] = {64, 64, 1};
+            if ((rc = avn_make_tmap(&tmA, d->A, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, 3, dims, str, box, true))) return rc;
+        }
     }
     // ---- B
     if (MODE == AVN_GEMM_NT) {
@@ -415,10 +443,19 @@ int launch(const avn_gemm_desc* d, cudaStream_t stream) {
         if ((rc = avn_make_tmap(&tmB, d->B, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, 3, dims, str, box, true))) return rc;
     } else {
         const int bb = tn ? d->batch : 1;
-        uint64_t dims[3] = {(uint64_t)d->N, (uint64_t)d->K, (uint64_t)bb};
-        uint64_t str[2] = {(uint64_t)d->ldb * 2, (uint64_t)(bb > 1 ? d->b_batch_stride : d->ldb * (int64_t)d->K) * 2};
-        uint32_t box[3] = {64, 64, 1};
-        if ((rc = avn_make_tmap(&tmB, d->B, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, 3, dims, str, box, true))) return rc;
+        const uint64_t bstr = (uint64_t)(bb > 1 ? d->b_batch_stride : d->ldb * (int64_t)d->K) * 2;
+        if (box4_ok(d->N)) {
+            uint64_t dims[4] = {64, (uint64_t)d->K, (uint64_t)d->N / 64, (uint64_t)bb};
+            uint64_t str[3] = {(uint64_t)d->ldb * 2, 128, bstr};
+            uint32_t box[4] = {64, 64, (uint32_t)(BN / CG / 64), 1};
+            b_box4 = avn_make_tmap(&tmB, d->B, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, 4, dims, str, box, true) == AVN_OK;
+        }
+        if (!b_box4) {
+            uint64_t dims[3] = {(uint64_t)d->N, (uint64_t)d->K, (uint64_t)bb};
+            uint64_t str[2] = {(uint64_t)d->ldb * 2, bstr};
+            uint32_t box[3] = {64, 64, 1};
+            if ((rc = avn_make_tmap(&tmB, d->B, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, 3, dims, str, box, true))) return rc;
+        }
     }
     // ---- C (and C2)
     const int cb = tn ? 1 : d->batch;
@@ -465,6 +502,7 @@ int launch(const avn_gemm_desc* d, cudaStream_t stream) {
     p.bias = d->bias;
     p.R = (const __nv_bfloat16*)d->R; p.ldr = d->ldr; p.r_batch_stride = d->r_batch_stride;
     p.colsum = tn ? d->colsum : nullptr;
+    p.a_box4 = a_box4; p.b_box4 = b_box4;
     const int total_tiles = (tn ? p.splits : d->batch) * ((p.m_tiles + CG - 1) / CG) * p.n_tiles;
     int grid = avn_num_sms() / CG;          // CTA pairs (or CTAs)
     if (grid > total_tiles) grid = total_tiles;
