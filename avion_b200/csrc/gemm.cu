@@ -25,6 +25,10 @@ constexpr int EPI_WARPS = 8;
 constexpr int NTHREADS = 64 + EPI_WARPS * 32;
 constexpr int A_STAGE_BYTES = BM * BK * 2;       // 16 KB
 constexpr int STG_BYTES = 128 * 128;             // one 128-row x 128-byte staging tile per epilogue group
+// which kernels may stage their R operand through shared memory (the single-CTA 256-wide kernel has no room for it)
+constexpr bool r_stageable(int BN, int EPI, int CG) {
+    return (EPI == AVN_EPI_BIAS_RESIDUAL || EPI == AVN_EPI_DGELU) && (CG == 2 || BN == 128);
+}
 
 struct KParams {
     int M, N, K, batch;
@@ -39,25 +43,28 @@ struct KParams {
 // CG = CTAs per MMA (cta_group): with CG = 2 a CTA pair computes a 256 x BN tile, each CTA staging its own 128 rows of A and
 // HALF of the B tile - the tensor core's shared-memory operand reads, which bound the single-CTA kernel at about two
 // thirds of the MMA rate, drop from 96 to 64 bytes per clock per SM.
-template <int BN, int CG>
+// RSTG: the epilogue reads a residual / gelu' tile (EPI_BIAS_RESIDUAL, EPI_DGELU) that TMA stages in shared memory, one
+// 128 x 64 tile per epilogue group; the CTA-pair kernels pay for it with one ring stage (5 instead of 6).
+template <int BN, int CG, bool RSTG>
 struct Smem {
-    static constexpr int STAGES = (CG == 2) ? 6 : 4;
+    static constexpr int STAGES = (CG == 2) ? (RSTG ? 5 : 6) : 4;
     static constexpr int B_STAGE_BYTES = (BN / CG) * BK * 2;
     static constexpr int OFF_A = 0;
     static constexpr int OFF_B = OFF_A + STAGES * A_STAGE_BYTES;
     static constexpr int OFF_STG = OFF_B + STAGES * B_STAGE_BYTES;
-    static constexpr int OFF_BIAS = OFF_STG + 2 * STG_BYTES;
+    static constexpr int OFF_RSTG = OFF_STG + 2 * STG_BYTES;
+    static constexpr int OFF_BIAS = OFF_RSTG + (RSTG ? 2 * STG_BYTES : 0);
     static constexpr int OFF_BAR = OFF_BIAS + BN * 4;
     static constexpr int TOTAL = OFF_BAR + 256 + 1024;   // + alignment slack
 };
 
-template <int BN, int MODE, int EPI, int CG>
+template <int BN, int MODE, int EPI, int CG, bool RS>
 __global__ void __launch_bounds__(NTHREADS, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
             const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmC2, const KParams p) {
     constexpr bool A_MN = (MODE == AVN_GEMM_TN);
     constexpr bool B_MN = (MODE != AVN_GEMM_NT);
-    using L = Smem<BN, CG>;
+    using L = Smem<BN, CG, RS>;
     constexpr int STAGES = L::STAGES;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
@@ -70,7 +77,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     uint64_t* tfull_bar = empty_bar + STAGES;
     uint64_t* tempty_bar = tfull_bar + 2;
     uint64_t* pfull_bar = tempty_bar + 2;       // column-sum mode, peer CTA of a pair: "stage is full", forwarded by the leader
-    uint32_t* tmem_ptr = (uint32_t*)(pfull_bar + STAGES);
+    uint64_t* rfull_bar = pfull_bar + STAGES;   // staged R tile of epilogue group 0 / 1 has landed
+    uint32_t* tmem_ptr = (uint32_t*)(rfull_bar + 2);
     const bool colsum_on = (MODE == AVN_GEMM_TN) && p.colsum != nullptr;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -82,7 +90,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         tma_prefetch_desc(&tmC);
         // column-sum mode: a stage is released by the MMA commit plus the arrive of epilogue warp 0
         for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], colsum_on ? 2 : 1); mbar_init(&pfull_bar[i], 1); }
-        for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], EPI_WARPS * CG); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], EPI_WARPS * CG); mbar_init(&rfull_bar[i], 1); }
         fence_barrier_init();
     }
     if (warp == 1) { if (CG == 2) tmem_alloc_2cta(tmem_ptr, 2 * BN); else tmem_alloc(tmem_ptr, 2 * BN); }
@@ -202,6 +210,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         constexpr int UNITS = BN / 2 / 32;      // 32-column units per group
         int acc = 0; uint32_t acc_phase = 0;
         int cs_stage = 0; uint32_t cs_phase = 0;
+        uint32_t r_phase = 0;
         for (int t = tile0; t < total_tiles; t += tile_step) {
             int n_blk = t % p.n_tiles; int r = t / p.n_tiles;
             int m_blk = (r % m_units) * CG + rank; int outer = r / m_units;
@@ -275,10 +284,23 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                 if (gtid < BN / 2) bias_s[gtid] = (p.bias != nullptr && n0 + gtid < p.N) ? p.bias[n0 + gtid] : 0.f;
                 named_bar_sync(bar_id, 128);
             }
-            // residual / pre-activation rows are fetched one 32-column unit ahead (the first one while the accumulator is
-            // still being computed): a row-per-thread global read has a long latency and nothing to hide behind otherwise
+            // Residual / gelu' tile (R).  Staged path (RS, chosen at launch when R meets TMA's alignment rules): TMA brings one 128 x 64
+            // tile per epilogue group into shared memory - the first one of an output tile is requested while the PREVIOUS
+            // tile's epilogue ends, the next one as soon as every thread holds its row of the current one - and a thread reads
+            // its row with eight 16-byte shared loads.  (Row-per-thread GLOBAL loads cost one L1 wavefront per row and load:
+            // ncu showed the L1 data pipe 75 % busy with them and the tensor pipe starved down to 74 % in the dgrad x gelu'
+            // GEMM.)  Fallback: those global loads, one 32-column unit ahead.
             constexpr bool HAS_R = (EPI == AVN_EPI_BIAS_RESIDUAL || EPI == AVN_EPI_DGELU);
+            uint8_t* rstg = smem + L::OFF_RSTG + g * STG_BYTES;
+            auto request_r = [&](int tile, int s64) {          // one thread per group: stage columns s64*64.. of `tile`
+                const int nb = tile % p.n_tiles, rr = tile / p.n_tiles;
+                const int mblk = (rr % m_units) * CG + rank, ob = rr / m_units;
+                mbar_expect_tx(&rfull_bar[g], STG_BYTES);
+                tma_load_3d(rstg, &tmC2, &rfull_bar[g], nb * BN + g * (BN / 2) + s64 * 64, mblk * BM, ob);
+            };
+            if (RS && t == tile0 && gtid == 0) request_r(t, 0);
             uint4 rnext[HAS_R ? 4 : 1];
+            uint4 rrow[RS ? 8 : 1];
             auto fetch_r = [&](int u) {
                 if (HAS_R) {
                     const int nc = n0 + u * 32;
@@ -290,7 +312,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                     }
                 }
             };
-            fetch_r(0);
+            if (!RS) fetch_r(0);
             mbar_wait(&tfull_bar[acc], acc_phase);
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN + g * (BN / 2);
@@ -332,9 +354,29 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                     }
                     if (HAS_R) {
                         uint4 rcur[4];
+                        if (RS) {
+                            if ((u & 1) == 0) {        // a new 64-column R tile: take this row of it, then let the next one come
+                                mbar_wait(&rfull_bar[g], r_phase);
+                                r_phase ^= 1;
 #pragma unroll
-                        for (int i = 0; i < 4; ++i) rcur[i] = rnext[i];
-                        if (u + 1 < UNITS) fetch_r(u + 1);
+                                for (int c = 0; c < 8; ++c) {
+                                    asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                                                 : "=r"(rrow[c].x), "=r"(rrow[c].y), "=r"(rrow[c].z), "=r"(rrow[c].w)
+                                                 : "r"(smem_u32(rstg) + row * 128 + ((c ^ (row & 7)) << 4)));
+                                }
+                                named_bar_sync(bar_id, 128);
+                                if (gtid == 0) {
+                                    if (u + 2 < UNITS) request_r(t, (u >> 1) + 1);
+                                    else if (t + tile_step < total_tiles) request_r(t + tile_step, 0);
+                                }
+                            }
+#pragma unroll
+                            for (int i = 0; i < 4; ++i) rcur[i] = rrow[(u & 1) * 4 + i];
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < 4; ++i) rcur[i] = rnext[i];
+                            if (u + 1 < UNITS) fetch_r(u + 1);
+                        }
 #pragma unroll
                         for (int i = 0; i < 4; ++i) {
                             const uint4 rv = rcur[i];
@@ -403,9 +445,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     if (warp == 1) { if (CG == 2) tmem_dealloc_2cta(tmem_base, 2 * BN); else tmem_dealloc(tmem_base, 2 * BN); }
 }
 
-template <int BN, int MODE, int EPI, int CG>
+template <int BN, int MODE, int EPI, int CG, bool RS>
 int launch(const avn_gemm_desc* d, cudaStream_t stream) {
-    using L = Smem<BN, CG>;
+    using L = Smem<BN, CG, RS>;
     CUtensorMap tmA, tmB, tmC, tmC2;
     const bool tn = (MODE == AVN_GEMM_TN);
     int rc;
@@ -503,11 +545,18 @@ int launch(const avn_gemm_desc* d, cudaStream_t stream) {
     p.R = (const __nv_bfloat16*)d->R; p.ldr = d->ldr; p.r_batch_stride = d->r_batch_stride;
     p.colsum = tn ? d->colsum : nullptr;
     p.a_box4 = a_box4; p.b_box4 = b_box4;
+    if (RS) {        // the R tile is staged by TMA (r_stage_ok() checked the alignment)
+        const int rb = d->batch;
+        uint64_t dims[3] = {(uint64_t)d->N, (uint64_t)d->M, (uint64_t)rb};
+        uint64_t str[2] = {(uint64_t)d->ldr * 2, (uint64_t)(rb > 1 ? d->r_batch_stride : d->ldr * (int64_t)d->M) * 2};
+        uint32_t box[3] = {64, 128, 1};
+        if ((rc = avn_make_tmap(&tmC2, d->R, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, 3, dims, str, box, true))) return rc;
+    }
     const int total_tiles = (tn ? p.splits : d->batch) * ((p.m_tiles + CG - 1) / CG) * p.n_tiles;
     int grid = avn_num_sms() / CG;          // CTA pairs (or CTAs)
     if (grid > total_tiles) grid = total_tiles;
     grid *= CG;
-    auto kern = gemm_kernel<BN, MODE, EPI, CG>;
+    auto kern = gemm_kernel<BN, MODE, EPI, CG, RS>;
     AVN_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(grid); cfg.blockDim = dim3(NTHREADS); cfg.dynamicSmemBytes = L::TOTAL; cfg.stream = stream;
@@ -517,6 +566,23 @@ int launch(const avn_gemm_desc* d, cudaStream_t stream) {
     cfg.attrs = attr; cfg.numAttrs = 1;
     AVN_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmC, tmC2, p));
     return AVN_OK;
+}
+
+// R through shared memory?  Only where TMA can address it (16-byte aligned rows; a table shared by all batch entries has
+// stride 0) and where it pays: the staged kernels give up one ring stage, and with a long contraction (fc2: K = 3072) the
+// row-per-thread loads are rare enough not to matter (2.74 ms vs 2.82 ms staged), so those keep the deeper ring.
+static bool r_stage_ok(const avn_gemm_desc* d, int epi) {
+    static const bool on = !(getenv("AVN_GEMM_RTMA") && atoi(getenv("AVN_GEMM_RTMA")) == 0);
+    if (!on || d->R == nullptr || ((uintptr_t)d->R % 16) != 0 || d->ldr % 8 != 0) return false;
+    if (d->batch > 1 && (d->r_batch_stride == 0 || d->r_batch_stride % 8 != 0)) return false;
+    return epi == AVN_EPI_DGELU || d->K <= 1536;
+}
+template <int BN, int MODE, int EPI, int CG>
+int launch_rs(const avn_gemm_desc* d, cudaStream_t stream) {
+    if constexpr (r_stageable(BN, EPI, CG)) {
+        if (r_stage_ok(d, EPI)) return launch<BN, MODE, EPI, CG, true>(d, stream);
+    }
+    return launch<BN, MODE, EPI, CG, false>(d, stream);
 }
 
 template <int MODE, int EPI>
@@ -532,10 +598,10 @@ int launch_bn(const avn_gemm_desc* d, cudaStream_t stream) {
     static const double tpair = getenv("AVN_GEMM_TPAIR") ? atof(getenv("AVN_GEMM_TPAIR")) : 1.5;
     if (d->N % 256 == 0 && (tiles256 >= t256 * avn_num_sms() || MODE == AVN_GEMM_TN)) {
         const bool pair_ok = (MODE == AVN_GEMM_TN) ? (d->M % 256 == 0) : (tiles256 >= tpair * avn_num_sms());
-        if (force_cg != 1 && pair_ok) return launch<256, MODE, EPI, 2>(d, stream);
-        return launch<256, MODE, EPI, 1>(d, stream);
+        if (force_cg != 1 && pair_ok) return launch_rs<256, MODE, EPI, 2>(d, stream);
+        return launch_rs<256, MODE, EPI, 1>(d, stream);
     }
-    return launch<128, MODE, EPI, 1>(d, stream);
+    return launch_rs<128, MODE, EPI, 1>(d, stream);
 }
 }  // namespace
 

@@ -38,7 +38,11 @@ else:
     a = (torch.randn(M, K, device="cuda") * 0.1).to(bf)
     b = (torch.randn(K, N, device="cuda") * 0.1).to(bf)
     c = torch.empty(M, N, dtype=bf, device="cuda")
-    fn = lambda: ops.gemm(ops.GEMM_NN, ops.EPI_NONE, M, N, K, a, K, b, N, c, N)      # noqa: E731
+    if os.environ.get("AVN_GEMM_EPI") == "dgelu":      # C = (A B) * R, R = gelu'(pre-activation) [M,N]
+        r = torch.rand(M, N, device="cuda").to(bf)
+        fn = lambda: ops.gemm(ops.GEMM_NN, ops.EPI_DGELU, M, N, K, a, K, b, N, c, N, R=r, ldr=N)      # noqa: E731
+    else:
+        fn = lambda: ops.gemm(ops.GEMM_NN, ops.EPI_NONE, M, N, K, a, K, b, N, c, N)      # noqa: E731
 for _ in range(2):
     fn()
 torch.cuda.synchronize()
