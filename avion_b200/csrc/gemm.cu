@@ -25,9 +25,10 @@ constexpr int EPI_WARPS = 8;
 constexpr int NTHREADS = 64 + EPI_WARPS * 32;
 constexpr int A_STAGE_BYTES = BM * BK * 2;       // 16 KB
 constexpr int STG_BYTES = 128 * 128;             // one 128-row x 128-byte staging tile per epilogue group
-// which kernels may stage their R operand through shared memory (the single-CTA 256-wide kernel has no room for it)
+// which kernels may use a second pair of staging tiles - for the R operand read by the epilogue, or for the second output of
+// the dual epilogue (the single-CTA 256-wide kernel has no room for it)
 constexpr bool r_stageable(int BN, int EPI, int CG) {
-    return (EPI == AVN_EPI_BIAS_RESIDUAL || EPI == AVN_EPI_DGELU) && (CG == 2 || BN == 128);
+    return (EPI == AVN_EPI_BIAS_RESIDUAL || EPI == AVN_EPI_DGELU || EPI == AVN_EPI_BIAS_GELU_DUAL) && (CG == 2 || BN == 128);
 }
 
 struct KParams {
@@ -43,8 +44,9 @@ struct KParams {
 // CG = CTAs per MMA (cta_group): with CG = 2 a CTA pair computes a 256 x BN tile, each CTA staging its own 128 rows of A and
 // HALF of the B tile - the tensor core's shared-memory operand reads, which bound the single-CTA kernel at about two
 // thirds of the MMA rate, drop from 96 to 64 bytes per clock per SM.
-// RSTG: the epilogue reads a residual / gelu' tile (EPI_BIAS_RESIDUAL, EPI_DGELU) that TMA stages in shared memory, one
-// 128 x 64 tile per epilogue group; the CTA-pair kernels pay for it with one ring stage (5 instead of 6).
+// RSTG: a second 128 x 64 staging tile per epilogue group - the residual / pre-activation tile (EPI_BIAS_RESIDUAL, EPI_DGELU)
+// that TMA brings in for the epilogue, or the second output of EPI_BIAS_GELU_DUAL on its way out; the CTA-pair kernels pay
+// for it with one ring stage (5 instead of 6).
 template <int BN, int CG, bool RSTG>
 struct Smem {
     static constexpr int STAGES = (CG == 2) ? (RSTG ? 5 : 6) : 4;
@@ -316,7 +318,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             mbar_wait(&tfull_bar[acc], acc_phase);
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN + g * (BN / 2);
-            uint32_t keep[(EPI == AVN_EPI_BIAS_GELU_DUAL) ? 32 : 1];
+            uint32_t keep[(EPI == AVN_EPI_BIAS_GELU_DUAL && !RS) ? 32 : 1];
 #pragma unroll
             for (int u = 0; u < UNITS; ++u) {
                 uint32_t v[32];
@@ -385,18 +387,33 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                             for (int e = 0; e < 4; ++e) {
                                 const float2 x = unpack_bf16(rr[e]);
                                 const float2 cur = make_float2(f[8 * i + 2 * e], f[8 * i + 2 * e + 1]);
-                                const float2 r = (EPI == AVN_EPI_BIAS_RESIDUAL) ? __fadd2_rn(cur, x) : __fmul2_rn(cur, x);     // DGELU: R holds gelu'(pre)
+                                // DGELU: R holds the bf16 pre-activation the forward kept (what autograd saves for GELU's backward)
+                                const float2 r = (EPI == AVN_EPI_BIAS_RESIDUAL) ? __fadd2_rn(cur, x) : __fmul2_rn(cur, gelu_erf_grad2(x));
                                 f[8 * i + 2 * e] = r.x; f[8 * i + 2 * e + 1] = r.y;
                             }
                         }
                     }
-                    if (EPI == AVN_EPI_BIAS_GELU_DUAL) {        // C = gelu(pre), C2 = gelu'(pre): what the backward of the MLP needs
+                    if (EPI == AVN_EPI_BIAS_GELU_DUAL) {        // C = gelu(pre), C2 = pre: what the backward of the MLP needs
+                        // (gelu' is evaluated by the EPI_DGELU epilogue of the dgrad GEMM, which has the issue slots to spare;
+                        // computing both here made this epilogue the bottleneck of the kernel: 3.57 ms vs 2.82 ms for gelu alone)
+#pragma unroll
+                        uint32_t xp[16];
 #pragma unroll
                         for (int j = 0; j < 16; ++j) {
-                            float2 g, dg;
-                            gelu_erf_both2(make_float2(f[2 * j], f[2 * j + 1]), g, dg);
-                            keep[(u & 1) * 16 + j] = pack_bf16(dg.x, dg.y);
+                            xp[j] = pack_bf16(f[2 * j], f[2 * j + 1]);
+                            if (!RS) keep[(u & 1) * 16 + j] = xp[j];
+                            const float2 g = gelu_erf2(make_float2(f[2 * j], f[2 * j + 1]));
                             f[2 * j] = g.x; f[2 * j + 1] = g.y;
+                        }
+                        if (RS) {       // second output -> its own staging tile; both tiles leave together below
+                            if ((u & 1) == 0) {
+                                if (gtid == 0) tma_wait_group_read0();
+                                named_bar_sync(bar_id, 128);
+                            }
+#pragma unroll
+                            for (int i = 0; i < 4; ++i)
+                                st_shared_v4(rstg + row * 128 + ((((u & 1) * 4 + i) ^ (row & 7)) << 4),
+                                             make_uint4(xp[4 * i], xp[4 * i + 1], xp[4 * i + 2], xp[4 * i + 3]));
                         }
                     }
                     if (EPI == AVN_EPI_BIAS_GELU) {
@@ -406,7 +423,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                             f[j] = g.x; f[j + 1] = g.y;
                         }
                     }
-                    if ((u & 1) == 0) {         // starting a new 64-column staging tile
+                    if ((u & 1) == 0 && !(EPI == AVN_EPI_BIAS_GELU_DUAL && RS)) {         // starting a new 64-column staging tile
                         if (gtid == 0) tma_wait_group_read0();
                         named_bar_sync(bar_id, 128);
                     }
@@ -420,8 +437,12 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                     if ((u & 1) == 1) {
                         fence_proxy_async_smem();
                         named_bar_sync(bar_id, 128);
-                        if (gtid == 0) { tma_store_3d(&tmC, stg, nc - 32, m0, mb); tma_commit_group(); }
-                        if (EPI == AVN_EPI_BIAS_GELU_DUAL) {
+                        if (gtid == 0) {
+                            tma_store_3d(&tmC, stg, nc - 32, m0, mb);
+                            if (EPI == AVN_EPI_BIAS_GELU_DUAL && RS) tma_store_3d(&tmC2, rstg, nc - 32, m0, mb);
+                            tma_commit_group();
+                        }
+                        if (EPI == AVN_EPI_BIAS_GELU_DUAL && !RS) {
                             if (gtid == 0) tma_wait_group_read0();
                             named_bar_sync(bar_id, 128);
 #pragma unroll
@@ -545,7 +566,7 @@ int launch(const avn_gemm_desc* d, cudaStream_t stream) {
     p.R = (const __nv_bfloat16*)d->R; p.ldr = d->ldr; p.r_batch_stride = d->r_batch_stride;
     p.colsum = tn ? d->colsum : nullptr;
     p.a_box4 = a_box4; p.b_box4 = b_box4;
-    if (RS) {        // the R tile is staged by TMA (r_stage_ok() checked the alignment)
+    if (RS && EPI != AVN_EPI_BIAS_GELU_DUAL) {        // the R tile is staged by TMA (r_stage_ok() checked the alignment)
         const int rb = d->batch;
         uint64_t dims[3] = {(uint64_t)d->N, (uint64_t)d->M, (uint64_t)rb};
         uint64_t str[2] = {(uint64_t)d->ldr * 2, (uint64_t)(rb > 1 ? d->r_batch_stride : d->ldr * (int64_t)d->M) * 2};
@@ -573,6 +594,7 @@ int launch(const avn_gemm_desc* d, cudaStream_t stream) {
 // row-per-thread loads are rare enough not to matter (2.74 ms vs 2.82 ms staged), so those keep the deeper ring.
 static bool r_stage_ok(const avn_gemm_desc* d, int epi) {
     static const bool on = !(getenv("AVN_GEMM_RTMA") && atoi(getenv("AVN_GEMM_RTMA")) == 0);
+    if (on && epi == AVN_EPI_BIAS_GELU_DUAL) return true;        // second output staged in its own tile: nothing to align
     if (!on || d->R == nullptr || ((uintptr_t)d->R % 16) != 0 || d->ldr % 8 != 0) return false;
     if (d->batch > 1 && (d->r_batch_stride == 0 || d->r_batch_stride % 8 != 0)) return false;
     return epi == AVN_EPI_DGELU || d->K <= 1536;
@@ -627,7 +649,7 @@ extern "C" int avn_gemm_bf16(const avn_gemm_desc* d, avn_stream_t stream_) {
         }
     } else if (d->mode == AVN_GEMM_NN) {
         AVN_REQUIRE(d->ldc % 8 == 0, "gemm: ldc must be a multiple of 8");
-        if (e == AVN_EPI_DGELU) AVN_REQUIRE(d->R != nullptr, "gemm: dgelu epilogue needs R (gelu' of the pre-activation)");
+        if (e == AVN_EPI_DGELU) AVN_REQUIRE(d->R != nullptr, "gemm: dgelu epilogue needs R (the pre-activation)");
         switch (e) {
             case AVN_EPI_NONE: return launch_bn<AVN_GEMM_NN, AVN_EPI_NONE>(d, stream);
             case AVN_EPI_DGELU: return launch_bn<AVN_GEMM_NN, AVN_EPI_DGELU>(d, stream);

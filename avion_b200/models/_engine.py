@@ -107,7 +107,7 @@ def blocks_backward(g, saved, layers, grads, heads, eps, causal, ws, last_colsum
             h = ws.get("h", (B, S, D), bf16, dev)
             ops.layernorm_fwd(x_mid, L["ln2_w"], L["ln2_b"], eps, out=h, save_stats=False)
         a = ws.get("a", (B, S, Hd), bf16, dev)
-        pre = ws.get("pre", (B, S, Hd), bf16, dev)      # receives gelu'(fc1 pre-activation)
+        pre = ws.get("pre", (B, S, Hd), bf16, dev)      # receives the fc1 pre-activation (gelu' is applied by the dgrad epilogue)
         ops.linear_fwd(h, L["fc1_w"], L["fc1_b"], EPI_BIAS_GELU_DUAL, out=a, out2=pre)
         # bias gradients = column sums of the incoming gradient: taken by the weight-gradient GEMM from the tiles it stages
         # anyway (FOLD_BIAS_GRAD; the two that feed a residual stream come out of the LayerNorm backward)

@@ -164,7 +164,7 @@ def linear_fwd(x, w, bias=None, epi=EPI_NONE, residual=None, out=None, out2=None
 
 
 def linear_dgrad(dy, w, epi=EPI_NONE, pre=None, out=None):
-    """dx[M,K] = epi(dy[M,N] @ w[N,K]); with EPI_DGELU: dx *= pre[M,K], where pre = gelu'(pre-activation) is the second
+    """dx[M,K] = epi(dy[M,N] @ w[N,K]); with EPI_DGELU: dx *= gelu'(pre[M,K]), where pre = the bf16 pre-activation, the second
     output of linear_fwd(..., EPI_BIAS_GELU_DUAL)."""
     _chk(dy, bf16, "dy"); _chk(w, bf16, "w")
     N, K = w.shape

@@ -241,15 +241,17 @@ def _linear_fake(x, w, bias=None, residual=None, act=0):
 
 
 def _linear_bwd(dy, x, w, bias, act, need_bias):
-    """-> (dx bf16, dw fp32 [N,K], dbias fp32 [N]); act == 1 recomputes gelu'(x w^T + b) with the dual epilogue."""
+    """-> (dx bf16, dw fp32 [N,K], dbias fp32 [N]); act == 1 recomputes the pre-activation x w^T + b with the dual epilogue."""
     Kd = x.shape[-1]
     M, N = x.numel() // Kd, w.shape[0]
     dev = x.device
     if act == 1:
         g = torch.empty(M, N, dtype=bf16, device=dev)
-        dg = torch.empty(M, N, dtype=bf16, device=dev)
-        K.gemm_bf16(GEMM_NT, EPI_BIAS_GELU_DUAL, M, N, Kd, 1, x, Kd, 0, w, Kd, 0, g, N, 0, dg, bias, None, N, 0, 1)
-        dy = (dy.reshape(M, N).float() * dg.float()).to(bf16)          # elementwise glue of the demo op only
+        pre = torch.empty(M, N, dtype=bf16, device=dev)
+        K.gemm_bf16(GEMM_NT, EPI_BIAS_GELU_DUAL, M, N, Kd, 1, x, Kd, 0, w, Kd, 0, g, N, 0, pre, bias, None, N, 0, 1)
+        pf = pre.float()                                                # elementwise glue of the demo op only: dy * gelu'(pre)
+        dgelu = 0.5 * (1.0 + torch.erf(pf * 0.7071067811865476)) + pf * torch.exp(-0.5 * pf * pf) * 0.3989422804014327
+        dy = (dy.reshape(M, N).float() * dgelu).to(bf16)
     dy = dy.reshape(M, N).contiguous()
     dx = torch.empty_like(x)
     K.gemm_bf16(GEMM_NN, EPI_NONE, M, Kd, N, 1, dy, N, 0, w, Kd, 0, dx, Kd, 0, None, None, None, Kd, 0, 1)

@@ -69,9 +69,10 @@ enum {
     AVN_EPI_NONE = 0,          /* C = acc                                   (bf16) */
     AVN_EPI_BIAS = 1,          /* C = acc + bias[n]                         (bf16) */
     AVN_EPI_BIAS_GELU = 2,     /* C = gelu(acc + bias[n])                   (bf16) */
-    AVN_EPI_BIAS_GELU_DUAL = 3,/* x = acc + bias[n]; C = gelu(x), C2 = gelu'(x) (bf16, bf16): C2 feeds AVN_EPI_DGELU */
+    AVN_EPI_BIAS_GELU_DUAL = 3,/* x = acc + bias[n]; C = gelu(x), C2 = x (bf16, bf16): C2 (the pre-activation autograd would
+                                  have saved, transformer.py:135) feeds AVN_EPI_DGELU */
     AVN_EPI_BIAS_RESIDUAL = 4, /* C = acc + bias[n] + R[m][n]               (bf16); bias may be NULL */
-    AVN_EPI_DGELU = 5,         /* C = acc * R[m][n], R = gelu'(pre) from AVN_EPI_BIAS_GELU_DUAL (bf16) */
+    AVN_EPI_DGELU = 5,         /* C = acc * gelu'(R[m][n]), R = pre-activation from AVN_EPI_BIAS_GELU_DUAL (bf16); exact-erf GELU */
     AVN_EPI_F32_ADD = 6        /* C += acc                                  (fp32, TMA reduce-add; split-K safe) */
 };
 typedef struct {

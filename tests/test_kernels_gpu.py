@@ -161,10 +161,8 @@ def test_gemm_nt_epilogues(ops, M, N, K):
     assert rel_err(ops.linear_fwd(x, w), acc) < 4e-3
     assert rel_err(ops.linear_fwd(x, w, bias, ops.EPI_BIAS), acc + bias) < 4e-3
     assert rel_err(ops.linear_fwd(x, w, bias, ops.EPI_BIAS_GELU), F.gelu(acc + bias)) < 5e-3
-    h, dgelu = ops.linear_fwd(x, w, bias, ops.EPI_BIAS_GELU_DUAL)      # gelu(pre) and gelu'(pre)
-    pre32 = (acc + bias).requires_grad_(True)
-    F.gelu(pre32).sum().backward()
-    assert rel_err(dgelu, pre32.grad) < 4e-3 and rel_err(h, F.gelu(acc + bias)) < 5e-3
+    h, pre = ops.linear_fwd(x, w, bias, ops.EPI_BIAS_GELU_DUAL)        # gelu(pre) and pre, what the MLP backward needs
+    assert rel_err(pre, acc + bias) < 4e-3 and rel_err(h, F.gelu(acc + bias)) < 5e-3
     assert rel_err(ops.linear_fwd(x, w, bias, ops.EPI_BIAS_RESIDUAL, residual=res), acc + bias + res.float()) < 4e-3
 
 
@@ -173,8 +171,10 @@ def test_gemm_nn_dgrad(ops, M, N, K):
     dy, w = rnd(M, N, seed=4), rnd(N, K, scale=N ** -0.5, seed=5)
     ref = dy.float() @ w.float()
     assert rel_err(ops.linear_dgrad(dy, w), ref) < 4e-3
-    dgelu = rnd(M, K, seed=6)            # stands for gelu'(pre), the second output of EPI_BIAS_GELU_DUAL
-    assert rel_err(ops.linear_dgrad(dy, w, ops.EPI_DGELU, pre=dgelu), ref * dgelu.float()) < 5e-3
+    pre = rnd(M, K, scale=1.5, seed=6)   # stands for the pre-activation, the second output of EPI_BIAS_GELU_DUAL
+    pre32 = pre.float().requires_grad_(True)
+    F.gelu(pre32).sum().backward()       # exact-erf gelu'
+    assert rel_err(ops.linear_dgrad(dy, w, ops.EPI_DGELU, pre=pre), ref * pre32.grad) < 5e-3
 
 
 @pytest.mark.parametrize("tok,N,K", [(512, 256, 128), (1000, 768, 768), (77 * 9, 384, 128), (128 * 150, 2304, 768), (333, 200, 72)])

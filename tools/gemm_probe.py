@@ -33,7 +33,15 @@ elif mode == "nt":
     a = (torch.randn(M, K, device="cuda") * 0.1).to(bf)
     b = (torch.randn(N, K, device="cuda") * 0.1).to(bf)
     c = torch.empty(M, N, dtype=bf, device="cuda")
-    fn = lambda: ops.gemm(ops.GEMM_NT, ops.EPI_NONE, M, N, K, a, K, b, K, c, N)      # noqa: E731
+    epi = os.environ.get("AVN_GEMM_EPI", "none")
+    bias = torch.randn(N, device="cuda")
+    if epi == "dual":
+        c2 = torch.empty(M, N, dtype=bf, device="cuda")
+        fn = lambda: ops.gemm(ops.GEMM_NT, ops.EPI_BIAS_GELU_DUAL, M, N, K, a, K, b, K, c, N, C2=c2, bias=bias)      # noqa: E731
+    elif epi == "gelu":
+        fn = lambda: ops.gemm(ops.GEMM_NT, ops.EPI_BIAS_GELU, M, N, K, a, K, b, K, c, N, bias=bias)      # noqa: E731
+    else:
+        fn = lambda: ops.gemm(ops.GEMM_NT, ops.EPI_NONE, M, N, K, a, K, b, K, c, N)      # noqa: E731
 else:
     a = (torch.randn(M, K, device="cuda") * 0.1).to(bf)
     b = (torch.randn(K, N, device="cuda") * 0.1).to(bf)
