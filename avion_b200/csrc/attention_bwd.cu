@@ -1,7 +1,7 @@
 // V4 backward: flash-style attention backward on tcgen05, head dim 64.
 // Replaces the backward of flash_attn_qkvpacked_func (avion/models/transformer.py:148) / nn.MultiheadAttention (:140-146).
 //
-// One CTA per (clip, head, 128-row K/V tile j); it loops over the query tiles i.  Everything is computed TRANSPOSED
+// One work item per (clip, head, 128-row K/V tile j): a loop over the query tiles i; persistent CTAs (one per SM) walk the items.  Everything is computed TRANSPOSED
 // (key rows on the TMEM lanes) so that P^T can feed the dV MMA straight from TMEM and dS^T is written to smem once:
 //   S^T  = K_j Q_i^T         dP^T = V_j dO_i^T                       (recompute; TMEM, 128 fp32 columns each)
 //   P^T  = exp(scale*S^T - LSE_q)           -> TMEM as bf16 (A operand of dV)
@@ -10,6 +10,7 @@
 //   dQ_i(partial) = dS K_j                                           (TMEM -> fp32 smem -> TMA reduce-add into dq_acc)
 // Warp roles (16 warps): 0-7 compute (thread = key row x half of the 128 query columns), 8-11 dQ drain,
 // 12 MMA issuer, 13 TMA producer, 14-15 idle (complete the warpgroup for setmaxnreg).
+#include <stdlib.h>
 #include "common.cuh"
 #include "../../include/avion_b200.h"
 
@@ -32,7 +33,8 @@ static_assert(SMEM_TOTAL <= 232448, "shared memory budget");
 constexpr uint32_t TM_S = 0, TM_DP = 128, TM_DV = 256, TM_DK = 320, TM_DQ = 384, TM_P = 448;
 
 struct Bars {
-    uint64_t kv_full, qdo_full[QDO_STAGES], qdo_empty[QDO_STAGES], sdp_full, sdp_free, p_ready, p_free, ds_ready[2], ds_free[2], dq_full, dq_free;
+    uint64_t kv_full, kv_free, acc_free, qdo_full[QDO_STAGES], qdo_empty[QDO_STAGES], sdp_full, sdp_free, p_ready, p_free, ds_ready[2],
+        ds_free[2], dq_full, dq_free;
     uint32_t tmem_ptr;
 };
 static_assert(sizeof(Bars) <= 256, "barrier block");
@@ -77,23 +79,30 @@ __device__ __forceinline__ void pds_chunk(const uint32_t* sv, const uint32_t* dv
     }
 }
 
+// Persistent: a CTA walks the work items (clip, head, K/V tile) item = blockIdx.x, += gridDim.x (K/V tile fastest, so the CTAs
+// of a wave share (clip, head) pairs and the dQ accumulator stays in L2).  Barriers, the Q/dO ring and the TMEM buffers are
+// set up once; every role counts its iterations globally (G), so barrier parities simply continue across items.  Between two
+// items the producer prefetches the next item's first Q/dO tiles while the last iterations still run, reloads K/V as soon as
+// the last MMAs have read them (kv_free), and that load overlaps the dK/dV drain of the finished item (acc_free tells the MMA
+// warp when dV/dK have left TMEM).  One CTA per item (gridDim.x = n_items) is the non-persistent schedule of the same code.
 __global__ void __launch_bounds__(NTHREADS, 1)
 attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
                 const __grid_constant__ CUtensorMap tmDQKV, const __grid_constant__ CUtensorMap tmDQ,
-                const float* __restrict__ lse, const float* __restrict__ delta, int S, int H, float scale, int causal) {
+                const float* __restrict__ lse, const float* __restrict__ delta, int S, int H, int n_items, float scale, int causal) {
     extern __shared__ __align__(1024) uint8_t smem[];
     Bars* bars = (Bars*)(smem + OFF_BAR);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int jt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
     const int q_tiles = (S + TILE - 1) / TILE;
-    const int i0 = causal ? jt : 0;
-    const int n_i = q_tiles - i0;
-    const int kv0 = jt * TILE;
+    // item -> (K/V tile, head, clip), first query tile and number of query tiles (causal: tiles on and below the diagonal)
+    auto decode = [&](int item, int& jt, int& h, int& b, int& i0, int& n_i) {
+        jt = item % q_tiles; const int r = item / q_tiles; h = r % H; b = r / H;
+        i0 = causal ? jt : 0; n_i = q_tiles - i0;
+    };
 
     if (threadIdx.x == 0) {
         if (smem_u32(smem) & 1023u) { printf("avion_b200: attn_bwd dynamic smem base not 1024-byte aligned\n"); __trap(); }
         tma_prefetch_desc(&tmQKV); tma_prefetch_desc(&tmDO); tma_prefetch_desc(&tmDQKV); tma_prefetch_desc(&tmDQ);
-        mbar_init(&bars->kv_full, 1);
+        mbar_init(&bars->kv_full, 1); mbar_init(&bars->kv_free, 1); mbar_init(&bars->acc_free, 256);
         for (int i = 0; i < QDO_STAGES; ++i) { mbar_init(&bars->qdo_full[i], 1); mbar_init(&bars->qdo_empty[i], 1); }
         for (int i = 0; i < 2; ++i) { mbar_init(&bars->ds_ready[i], 256); mbar_init(&bars->ds_free[i], 1); }
         mbar_init(&bars->sdp_full, 1); mbar_init(&bars->sdp_free, 256);
@@ -113,56 +122,72 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
         // ===================== TMA producer =====================
         // (whole warp loops and waits; one elected lane issues, so addresses and coordinates stay in uniform registers)
         reg_dec<40>();
-        if (elect_one()) {
-            mbar_expect_tx(&bars->kv_full, 2 * T16);
-            tma_load_3d(smem + OFF_K, &tmQKV, &bars->kv_full, (H + h) * HD, kv0, b);
-            tma_load_3d(smem + OFF_V, &tmQKV, &bars->kv_full, (2 * H + h) * HD, kv0, b);
-        }
-        __syncwarp();
-        for (int t = 0; t < n_i; ++t) {
-            const int st = t % QDO_STAGES;
-            mbar_wait(&bars->qdo_empty[st], ((t / QDO_STAGES) & 1) ^ 1);
+        int G0 = 0, it = 0;
+        for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
+            int jt, h, b, i0, n_i;
+            decode(item, jt, h, b, i0, n_i);
+            auto load_qdo = [&](int t) {
+                const int G = G0 + t, st = G % QDO_STAGES;
+                mbar_wait(&bars->qdo_empty[st], ((G / QDO_STAGES) & 1) ^ 1);
+                if (elect_one()) {
+                    mbar_expect_tx(&bars->qdo_full[st], 2 * T16);
+                    tma_load_3d(smem + OFF_Q + st * T16, &tmQKV, &bars->qdo_full[st], h * HD, (i0 + t) * TILE, b);
+                    tma_load_3d(smem + OFF_DO + st * T16, &tmDO, &bars->qdo_full[st], h * HD, (i0 + t) * TILE, b);
+                }
+                __syncwarp();
+            };
+            // the first Q/dO tiles go into ring slots as the previous item's last iterations release them; K/V can only
+            // follow the previous item's last MMA
+            const int head = min(n_i, QDO_STAGES);
+            for (int t = 0; t < head; ++t) load_qdo(t);
+            if (it > 0) mbar_wait(&bars->kv_free, (it - 1) & 1);
             if (elect_one()) {
-                mbar_expect_tx(&bars->qdo_full[st], 2 * T16);
-                tma_load_3d(smem + OFF_Q + st * T16, &tmQKV, &bars->qdo_full[st], h * HD, (i0 + t) * TILE, b);
-                tma_load_3d(smem + OFF_DO + st * T16, &tmDO, &bars->qdo_full[st], h * HD, (i0 + t) * TILE, b);
+                mbar_expect_tx(&bars->kv_full, 2 * T16);
+                tma_load_3d(smem + OFF_K, &tmQKV, &bars->kv_full, (H + h) * HD, jt * TILE, b);
+                tma_load_3d(smem + OFF_V, &tmQKV, &bars->kv_full, (2 * H + h) * HD, jt * TILE, b);
             }
             __syncwarp();
+            for (int t = head; t < n_i; ++t) load_qdo(t);
+            G0 += n_i;
         }
     } else if (warp == 12) {
         // ===================== MMA issuer =====================
         // waits are executed by the whole warp, the MMAs by one elected lane (descriptors stay in uniform registers)
         reg_dec<40>();
-        if (n_i > 0) {
-            constexpr uint32_t idesc_s = umma_idesc_bf16(TILE, TILE, false, false);
-            constexpr uint32_t idesc_kn = umma_idesc_bf16(TILE, HD, false, true);    // A K-major (or TMEM), B MN-major
-            constexpr uint32_t idesc_nn = umma_idesc_bf16(TILE, HD, true, true);     // A MN-major, B MN-major
-            const uint32_t ka = smem_u32(smem + OFF_K), va = smem_u32(smem + OFF_V);
-            auto issue_sdp = [&](int t) {
-                const int st = t % QDO_STAGES;
-                mbar_wait(&bars->qdo_full[st], (t / QDO_STAGES) & 1);
-                if (t > 0) mbar_wait(&bars->sdp_free, (t - 1) & 1);
-                tc_fence_after();
-                if (elect_one()) {
-                    const uint32_t qa = smem_u32(smem + OFF_Q + st * T16), doa = smem_u32(smem + OFF_DO + st * T16);
+        constexpr uint32_t idesc_s = umma_idesc_bf16(TILE, TILE, false, false);
+        constexpr uint32_t idesc_kn = umma_idesc_bf16(TILE, HD, false, true);    // A K-major (or TMEM), B MN-major
+        constexpr uint32_t idesc_nn = umma_idesc_bf16(TILE, HD, true, true);     // A MN-major, B MN-major
+        const uint32_t ka = smem_u32(smem + OFF_K), va = smem_u32(smem + OFF_V);
+        auto issue_sdp = [&](int G) {
+            const int st = G % QDO_STAGES;
+            mbar_wait(&bars->qdo_full[st], (G / QDO_STAGES) & 1);
+            if (G > 0) mbar_wait(&bars->sdp_free, (G - 1) & 1);
+            tc_fence_after();
+            if (elect_one()) {
+                const uint32_t qa = smem_u32(smem + OFF_Q + st * T16), doa = smem_u32(smem + OFF_DO + st * T16);
 #pragma unroll
-                    for (int k = 0; k < HD / 16; ++k)      // S^T = K Q^T
-                        umma_ss(tmem_base + TM_S, umma_smem_desc(ka + k * 32, 16, 1024), umma_smem_desc(qa + k * 32, 16, 1024), idesc_s, k > 0);
+                for (int k = 0; k < HD / 16; ++k)      // S^T = K Q^T
+                    umma_ss(tmem_base + TM_S, umma_smem_desc(ka + k * 32, 16, 1024), umma_smem_desc(qa + k * 32, 16, 1024), idesc_s, k > 0);
 #pragma unroll
-                    for (int k = 0; k < HD / 16; ++k)      // dP^T = V dO^T
-                        umma_ss(tmem_base + TM_DP, umma_smem_desc(va + k * 32, 16, 1024), umma_smem_desc(doa + k * 32, 16, 1024), idesc_s, k > 0);
-                    umma_commit(&bars->sdp_full);
-                }
-                __syncwarp();
-            };
-            mbar_wait(&bars->kv_full, 0);
-            issue_sdp(0);
+                for (int k = 0; k < HD / 16; ++k)      // dP^T = V dO^T
+                    umma_ss(tmem_base + TM_DP, umma_smem_desc(va + k * 32, 16, 1024), umma_smem_desc(doa + k * 32, 16, 1024), idesc_s, k > 0);
+                umma_commit(&bars->sdp_full);
+            }
+            __syncwarp();
+        };
+        int G0 = 0, it = 0;
+        for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
+            int jt, h, b, i0, n_i;
+            decode(item, jt, h, b, i0, n_i);
+            mbar_wait(&bars->kv_full, it & 1);
+            issue_sdp(G0);
             for (int t = 0; t < n_i; ++t) {
-                const int st = t % QDO_STAGES, db = t & 1;
-                if (t + 1 < n_i) issue_sdp(t + 1);
+                const int G = G0 + t, st = G % QDO_STAGES, db = G & 1;
+                if (t + 1 < n_i) issue_sdp(G + 1);
                 const uint32_t qa = smem_u32(smem + OFF_Q + st * T16), doa = smem_u32(smem + OFF_DO + st * T16);
                 const uint32_t dsa = smem_u32(smem + OFF_DS + db * 2 * T16);
-                mbar_wait(&bars->p_ready, t & 1);
+                mbar_wait(&bars->p_ready, G & 1);
+                if (t == 0 && it > 0) mbar_wait(&bars->acc_free, (it - 1) & 1);     // the previous item's dV / dK have left TMEM
                 tc_fence_after();
                 if (elect_one()) {
 #pragma unroll
@@ -172,7 +197,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
                     umma_commit(&bars->p_free);
                 }
                 __syncwarp();
-                mbar_wait(&bars->ds_ready[db], (t >> 1) & 1);
+                mbar_wait(&bars->ds_ready[db], (G >> 1) & 1);
                 tc_fence_after();
                 if (elect_one()) {
 #pragma unroll
@@ -182,7 +207,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
                     umma_commit(&bars->qdo_empty[st]);       // Q_t / dO_t are not read after dK
                 }
                 __syncwarp();
-                if (t > 0) { mbar_wait(&bars->dq_free, (t - 1) & 1); tc_fence_after(); }   // dQ_{t-1} has left TMEM
+                if (G > 0) { mbar_wait(&bars->dq_free, (G - 1) & 1); tc_fence_after(); }   // the previous dQ tile has left TMEM
                 if (elect_one()) {
 #pragma unroll
                     for (int k = 0; k < TILE / 16; ++k)      // dQ_i = dS K_j  (A = dS^T bytes read MN-major, B = K_j MN-major)
@@ -190,9 +215,11 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
                                 umma_smem_desc(ka + k * 2048, 8192, 1024), idesc_nn, k > 0 ? 1u : 0u);
                     umma_commit(&bars->dq_full);
                     umma_commit(&bars->ds_free[db]);
+                    if (t == n_i - 1) umma_commit(&bars->kv_free);       // every MMA of the item has read K / V
                 }
                 __syncwarp();
             }
+            G0 += n_i;
         }
     } else if (warp >= 8) {
         // ===================== dQ drain: TMEM -> fp32 staging -> TMA reduce-add =====================
@@ -200,135 +227,153 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
         const int row = (warp & 3) * 32 + lane;
         const uint32_t lane_addr = (uint32_t)((warp & 3) * 32) << 16;
         const bool leader = (threadIdx.x == 256);
-        for (int t = 0; t < n_i; ++t) {
-            mbar_wait(&bars->dq_full, t & 1);
-            tc_fence_after();
-            uint32_t v[64];
-            tmem_ld32(tmem_base + lane_addr + TM_DQ, v);
-            tmem_ld32(tmem_base + lane_addr + TM_DQ + 32, v + 32);
-            tmem_ld_wait();
-            tc_fence_before();
-            mbar_arrive(&bars->dq_free);
-            uint8_t* stg = smem + OFF_STG;
-            if (t >= 1) {                            // the reduce of tile t-1 must have finished reading the staging tile
-                if (leader) tma_wait_group_read0();
+        int G0 = 0;
+        for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+            int jt, h, b, i0, n_i;
+            decode(item, jt, h, b, i0, n_i);
+            for (int t = 0; t < n_i; ++t) {
+                const int G = G0 + t;
+                mbar_wait(&bars->dq_full, G & 1);
+                tc_fence_after();
+                uint32_t v[64];
+                tmem_ld32(tmem_base + lane_addr + TM_DQ, v);
+                tmem_ld32(tmem_base + lane_addr + TM_DQ + 32, v + 32);
+                tmem_ld_wait();
+                tc_fence_before();
+                mbar_arrive(&bars->dq_free);
+                uint8_t* stg = smem + OFF_STG;
+                if (G >= 1) {                            // the reduce of the previous tile must have finished reading the staging tile
+                    if (leader) tma_wait_group_read0();
+                    named_bar_sync(2, 128);
+                }
+#pragma unroll
+                for (int c = 0; c < 2; ++c)
+#pragma unroll
+                    for (int i = 0; i < 8; ++i)
+                        st_shared_v4(stg + c * T16 + row * 128 + ((i ^ (row & 7)) << 4),
+                                     make_uint4(v[c * 32 + 4 * i], v[c * 32 + 4 * i + 1], v[c * 32 + 4 * i + 2], v[c * 32 + 4 * i + 3]));
+                fence_proxy_async_smem();
                 named_bar_sync(2, 128);
+                if (leader) {
+                    tma_reduce_add_3d(&tmDQ, stg, h * HD, (i0 + t) * TILE, b);
+                    tma_reduce_add_3d(&tmDQ, stg + T16, h * HD + 32, (i0 + t) * TILE, b);
+                    tma_commit_group();
+                }
             }
-#pragma unroll
-            for (int c = 0; c < 2; ++c)
-#pragma unroll
-                for (int i = 0; i < 8; ++i)
-                    st_shared_v4(stg + c * T16 + row * 128 + ((i ^ (row & 7)) << 4),
-                                 make_uint4(v[c * 32 + 4 * i], v[c * 32 + 4 * i + 1], v[c * 32 + 4 * i + 2], v[c * 32 + 4 * i + 3]));
-            fence_proxy_async_smem();
-            named_bar_sync(2, 128);
-            if (leader) {
-                tma_reduce_add_3d(&tmDQ, stg, h * HD, (i0 + t) * TILE, b);
-                tma_reduce_add_3d(&tmDQ, stg + T16, h * HD + 32, (i0 + t) * TILE, b);
-                tma_commit_group();
-            }
+            G0 += n_i;
         }
         if (leader) tma_wait_group0();
     } else {
         // ===================== compute warps: thread = (key row, half of the query columns) =====================
         reg_inc<192>();
-        if (n_i > 0) {
         const int half = warp >> 2;
         const int row = (warp & 3) * 32 + lane;
         const uint32_t lane_addr = (uint32_t)((warp & 3) * 32) << 16;
         const float scale_log2 = scale * 1.4426950408889634f;
-        const long long stat_base = ((long long)b * H + h) * S;
         float* stat = (float*)(smem + OFF_STAT);
-        // per-query-row statistics of tile t live in stat[(t&1)*256 ...]: threads 0-127 own -lse*log2e, 128-255 own -delta*scale
+        // per-query-row statistics of iteration G live in stat[(G&1)*256 ...]: threads 0-127 own -lse*log2e, 128-255 own -delta*scale
         const int sidx = threadIdx.x & 127;
         const bool own_lse = threadIdx.x < 128;
-        // the raw global value is kept in a register for a whole tile and only converted when it is stored: the use of
-        // a load result is what stalls, so the conversion must not sit right behind the load
-        const float* stat_src = (own_lse ? lse : delta) + stat_base;
         const float stat_mul = own_lse ? -1.4426950408889634f : -scale;
-        auto load_stat = [&](int t) -> float {
-            const int qr = (i0 + t) * TILE + sidx;
-            return qr < S ? __ldg(stat_src + qr) : (own_lse ? INFINITY : 0.f);      // -inf after scaling: P = 0 past the end
-        };
-        stat[threadIdx.x] = load_stat(0) * stat_mul;
-        float stat_nx = n_i > 1 ? load_stat(1) : 0.f;
+        int G0 = 0;
+        for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+            int jt, h, b, i0, n_i;
+            decode(item, jt, h, b, i0, n_i);
+            const int kv0 = jt * TILE;
+            // the raw global value is kept in a register for a whole tile and only converted when it is stored: the use of
+            // a load result is what stalls, so the conversion must not sit right behind the load
+            const float* stat_src = (own_lse ? lse : delta) + ((long long)b * H + h) * S;
+            auto load_stat = [&](int t) -> float {
+                const int qr = (i0 + t) * TILE + sidx;
+                return qr < S ? __ldg(stat_src + qr) : (own_lse ? INFINITY : 0.f);      // -inf after scaling: P = 0 past the end
+            };
+            // (buffer G0&1 was last read in iteration G0-2; every thread has passed the barrier of iteration G0-1 since)
+            stat[(G0 & 1) * 256 + threadIdx.x] = load_stat(0) * stat_mul;
+            float stat_nx = n_i > 1 ? load_stat(1) : 0.f;
 
-        for (int t = 0; t < n_i; ++t) {
-            const int buf = t & 1;
-            const int q0 = (i0 + t) * TILE;
-            const bool need_mask = causal && (q0 < kv0 + TILE - 1);      // diagonal tile of the causal text tower (warp-uniform)
-            mbar_wait(&bars->sdp_full, t & 1);
+            for (int t = 0; t < n_i; ++t) {
+                const int G = G0 + t;
+                const int buf = G & 1;
+                const int q0 = (i0 + t) * TILE;
+                const bool need_mask = causal && (q0 < kv0 + TILE - 1);      // diagonal tile of the causal text tower (warp-uniform)
+                mbar_wait(&bars->sdp_full, G & 1);
+                tc_fence_after();
+                named_bar_sync(1, 256);           // stat[buf] is complete; nobody still reads stat[buf^1] (previous iteration)
+                if (t + 1 < n_i) {
+                    stat[(buf ^ 1) * 256 + threadIdx.x] = stat_nx * stat_mul;
+                    if (t + 2 < n_i) stat_nx = load_stat(t + 2);
+                }
+                const float* nl = stat + buf * 256 + half * 64;
+                const float* nd = nl + 128;
+                uint32_t pk[32], dsk[32];     // packed bf16: 64 P^T values and 64 dS^T values of this thread
+#pragma unroll
+                for (int c = 0; c < 2; ++c) {
+                    uint32_t sv[32], dv[32];
+                    tmem_ld32(tmem_base + lane_addr + TM_S + half * 64 + c * 32, sv);
+                    tmem_ld32(tmem_base + lane_addr + TM_DP + half * 64 + c * 32, dv);
+                    tmem_ld_wait();
+                    if (c == 1) { tc_fence_before(); mbar_arrive(&bars->sdp_free); }
+                    // causal: key kv0+row is visible to query q0+col iff col >= kv0 + row - q0
+                    const int first_valid = kv0 + row - q0 - (half * 64 + c * 32);
+                    if (need_mask) pds_chunk<true>(sv, dv, pk + c * 16, dsk + c * 16, nl + c * 32, nd + c * 32, scale_log2, scale, first_valid);
+                    else pds_chunk<false>(sv, dv, pk + c * 16, dsk + c * 16, nl + c * 32, nd + c * 32, scale_log2, scale, 0);
+                }
+                // dS^T -> smem [kv][q]: buffer G&1 was last read by the dK/dQ MMAs of iteration G-2.  The stores are issued first
+                // and complete while P^T goes to TMEM.
+                if (G >= 2) mbar_wait(&bars->ds_free[buf], ((G >> 1) - 1) & 1);
+                uint8_t* drow = smem + OFF_DS + buf * 2 * T16 + half * T16 + row * 128;
+#pragma unroll
+                for (int i = 0; i < 8; ++i)
+                    st_shared_v4(drow + ((i ^ (row & 7)) << 4), make_uint4(dsk[4 * i], dsk[4 * i + 1], dsk[4 * i + 2], dsk[4 * i + 3]));
+                // P^T -> TMEM (bf16 pairs, lane = key row): the previous dV MMA must have finished reading the previous P^T
+                if (G > 0) { mbar_wait(&bars->p_free, (G - 1) & 1); tc_fence_after(); }
+                tmem_st32(tmem_base + lane_addr + TM_P + half * 32, pk);
+                tmem_st_wait();
+                tc_fence_before();
+                mbar_arrive(&bars->p_ready);
+                fence_proxy_async_smem();
+                mbar_arrive(&bars->ds_ready[buf]);
+            }
+            // every MMA of the item has completed once the last ds_free fires (it is committed after dQ of the last tile)
+            const int Gl = G0 + n_i - 1;
+            mbar_wait(&bars->ds_free[Gl & 1], (Gl >> 1) & 1);
             tc_fence_after();
-            named_bar_sync(1, 256);           // stat[buf] is complete; nobody still reads stat[buf^1] (tile t-1)
-            if (t + 1 < n_i) {
-                stat[(buf ^ 1) * 256 + threadIdx.x] = stat_nx * stat_mul;
-                if (t + 2 < n_i) stat_nx = load_stat(t + 2);
-            }
-            const float* nl = stat + buf * 256 + half * 64;
-            const float* nd = nl + 128;
-            uint32_t pk[32], dsk[32];     // packed bf16: 64 P^T values and 64 dS^T values of this thread
-#pragma unroll
-            for (int c = 0; c < 2; ++c) {
-                uint32_t sv[32], dv[32];
-                tmem_ld32(tmem_base + lane_addr + TM_S + half * 64 + c * 32, sv);
-                tmem_ld32(tmem_base + lane_addr + TM_DP + half * 64 + c * 32, dv);
+            // dV, dK: TMEM -> bf16 -> swizzled smem (the dS buffers are free now) -> TMA store
+            {
+                uint32_t v[32], k[32];
+                tmem_ld32(tmem_base + lane_addr + TM_DV + half * 32, v);
+                tmem_ld32(tmem_base + lane_addr + TM_DK + half * 32, k);
                 tmem_ld_wait();
-                if (c == 1) { tc_fence_before(); mbar_arrive(&bars->sdp_free); }
-                // causal: key kv0+row is visible to query q0+col iff col >= kv0 + row - q0
-                const int first_valid = kv0 + row - q0 - (half * 64 + c * 32);
-                if (need_mask) pds_chunk<true>(sv, dv, pk + c * 16, dsk + c * 16, nl + c * 32, nd + c * 32, scale_log2, scale, first_valid);
-                else pds_chunk<false>(sv, dv, pk + c * 16, dsk + c * 16, nl + c * 32, nd + c * 32, scale_log2, scale, 0);
-            }
-            // dS^T -> smem [kv][q]: buffer t&1 was last read by the dK/dQ MMAs of tile t-2.  The stores are issued first and
-            // complete while P^T goes to TMEM.
-            if (t >= 2) mbar_wait(&bars->ds_free[buf], ((t >> 1) - 1) & 1);
-            uint8_t* drow = smem + OFF_DS + buf * 2 * T16 + half * T16 + row * 128;
+                tc_fence_before();
+                mbar_arrive(&bars->acc_free);          // the next item may start accumulating dV / dK
+                uint8_t* vrow = smem + OFF_DS + row * 128;
+                uint8_t* krow = smem + OFF_DS + 2 * T16 + row * 128;
 #pragma unroll
-            for (int i = 0; i < 8; ++i)
-                st_shared_v4(drow + ((i ^ (row & 7)) << 4), make_uint4(dsk[4 * i], dsk[4 * i + 1], dsk[4 * i + 2], dsk[4 * i + 3]));
-            // P^T -> TMEM (bf16 pairs, lane = key row): dV_{t-1} must have finished reading the previous P^T
-            if (t > 0) { mbar_wait(&bars->p_free, (t - 1) & 1); tc_fence_after(); }
-            tmem_st32(tmem_base + lane_addr + TM_P + half * 32, pk);
-            tmem_st_wait();
-            tc_fence_before();
-            mbar_arrive(&bars->p_ready);
-            fence_proxy_async_smem();
-            mbar_arrive(&bars->ds_ready[buf]);
-        }
-        // every MMA has completed once the last ds_free fires (it is committed after dQ of the last tile)
-        mbar_wait(&bars->ds_free[(n_i - 1) & 1], ((n_i - 1) >> 1) & 1);
-        tc_fence_after();
-        // dV, dK: TMEM -> bf16 -> swizzled smem (the dS buffers are free now) -> TMA store
-        {
-            uint32_t v[32], k[32];
-            tmem_ld32(tmem_base + lane_addr + TM_DV + half * 32, v);
-            tmem_ld32(tmem_base + lane_addr + TM_DK + half * 32, k);
-            tmem_ld_wait();
-            tc_fence_before();
-            uint8_t* vrow = smem + OFF_DS + row * 128;
-            uint8_t* krow = smem + OFF_DS + 2 * T16 + row * 128;
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const int off = ((half * 4 + i) ^ (row & 7)) << 4;
-                st_shared_v4(vrow + off, make_uint4(pack_bf16(__uint_as_float(v[8 * i]), __uint_as_float(v[8 * i + 1])),
-                                                    pack_bf16(__uint_as_float(v[8 * i + 2]), __uint_as_float(v[8 * i + 3])),
-                                                    pack_bf16(__uint_as_float(v[8 * i + 4]), __uint_as_float(v[8 * i + 5])),
-                                                    pack_bf16(__uint_as_float(v[8 * i + 6]), __uint_as_float(v[8 * i + 7]))));
-                st_shared_v4(krow + off, make_uint4(pack_bf16(__uint_as_float(k[8 * i]), __uint_as_float(k[8 * i + 1])),
-                                                    pack_bf16(__uint_as_float(k[8 * i + 2]), __uint_as_float(k[8 * i + 3])),
-                                                    pack_bf16(__uint_as_float(k[8 * i + 4]), __uint_as_float(k[8 * i + 5])),
-                                                    pack_bf16(__uint_as_float(k[8 * i + 6]), __uint_as_float(k[8 * i + 7]))));
+                for (int i = 0; i < 4; ++i) {
+                    const int off = ((half * 4 + i) ^ (row & 7)) << 4;
+                    st_shared_v4(vrow + off, make_uint4(pack_bf16(__uint_as_float(v[8 * i]), __uint_as_float(v[8 * i + 1])),
+                                                        pack_bf16(__uint_as_float(v[8 * i + 2]), __uint_as_float(v[8 * i + 3])),
+                                                        pack_bf16(__uint_as_float(v[8 * i + 4]), __uint_as_float(v[8 * i + 5])),
+                                                        pack_bf16(__uint_as_float(v[8 * i + 6]), __uint_as_float(v[8 * i + 7]))));
+                    st_shared_v4(krow + off, make_uint4(pack_bf16(__uint_as_float(k[8 * i]), __uint_as_float(k[8 * i + 1])),
+                                                        pack_bf16(__uint_as_float(k[8 * i + 2]), __uint_as_float(k[8 * i + 3])),
+                                                        pack_bf16(__uint_as_float(k[8 * i + 4]), __uint_as_float(k[8 * i + 5])),
+                                                        pack_bf16(__uint_as_float(k[8 * i + 6]), __uint_as_float(k[8 * i + 7]))));
+                }
+                fence_proxy_async_smem();
+                named_bar_sync(1, 256);
+                if (threadIdx.x == 0) {
+                    tma_store_3d(&tmDQKV, smem + OFF_DS + 2 * T16, (H + h) * HD, kv0, b);
+                    tma_store_3d(&tmDQKV, smem + OFF_DS, (2 * H + h) * HD, kv0, b);
+                    tma_commit_group();
+                    // the dS buffers are rewritten in the next item's first iterations, behind that iteration's barrier (which
+                    // this thread only reaches after the stores have read them)
+                    tma_wait_group_read0();
+                }
             }
-            fence_proxy_async_smem();
-            named_bar_sync(1, 256);
-            if (threadIdx.x == 0) {
-                tma_store_3d(&tmDQKV, smem + OFF_DS + 2 * T16, (H + h) * HD, kv0, b);
-                tma_store_3d(&tmDQKV, smem + OFF_DS, (2 * H + h) * HD, kv0, b);
-                tma_commit_group();
-                tma_wait_group0();
-            }
+            G0 += n_i;
         }
-        }   // n_i > 0
+        if (threadIdx.x == 0) tma_wait_group0();
     }
     tc_fence_before();
     __syncthreads();
@@ -401,7 +446,12 @@ extern "C" int avn_attn_bwd(const void* qkv, const void* out, const void* dout, 
     AVN_CHECK_CUDA(cudaGetLastError());
     const int tiles = (S + TILE - 1) / TILE;
     AVN_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_TOTAL));
-    attn_bwd_kernel<<<dim3(tiles, H, B), NTHREADS, SMEM_TOTAL, stream>>>(tmQKV, tmDO, tmDQKV, tmDQ, lse, delta, S, H, scale, causal);
+    // one CTA per SM walking the items; AVN_ATTN_BWD_PERSIST=0: one CTA per item (A/B runs)
+    static const bool persist = !(getenv("AVN_ATTN_BWD_PERSIST") && atoi(getenv("AVN_ATTN_BWD_PERSIST")) == 0);
+    const long long n_items = (long long)tiles * H * B;
+    AVN_REQUIRE(n_items < (1ll << 31), "attn_bwd: too many work items");
+    const int grid = persist ? (int)(n_items < avn_num_sms() ? n_items : avn_num_sms()) : (int)n_items;
+    attn_bwd_kernel<<<grid, NTHREADS, SMEM_TOTAL, stream>>>(tmQKV, tmDO, tmDQKV, tmDQ, lse, delta, S, H, (int)n_items, scale, causal);
     AVN_CHECK_CUDA(cudaGetLastError());
     const long long nvec = rows * (W1 / 8);
     dq_convert_kernel<<<(unsigned)((nvec + 255) / 256), 256, 0, stream>>>(dq_acc, (__nv_bfloat16*)dqkv, rows, (int)W1);
