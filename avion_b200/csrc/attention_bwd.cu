@@ -368,12 +368,13 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
                     tma_commit_group();
                     // the dS buffers are rewritten in the next item's first iterations, behind that iteration's barrier (which
                     // this thread only reaches after the stores have read them)
-                    tma_wait_group_read0();
+                    // (the last item waits for full completion here: a wait placed after the item loop makes ptxas compile this
+                    // branch for the kernel-wide 128 registers instead of the 192 the warpgroups have)
+                    if (item + (int)gridDim.x >= n_items) tma_wait_group0(); else tma_wait_group_read0();
                 }
             }
             G0 += n_i;
         }
-        if (threadIdx.x == 0) tma_wait_group0();
     }
     tc_fence_before();
     __syncthreads();

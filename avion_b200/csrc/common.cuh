@@ -77,7 +77,7 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 #ifndef AVN_SPIN_LOG2
-#define AVN_SPIN_LOG2 26
+#define AVN_SPIN_LOG2 23
 #endif
 // Bounded spin: a protocol bug traps (kernel error) instead of hanging the GPU.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
