@@ -232,7 +232,10 @@ def attn_ref(qkv, H, scale, causal):
 
 
 @pytest.mark.parametrize("B,S,H,causal", [(2, 128, 2, False), (2, 65, 2, False), (3, 785, 3, False), (1, 3137, 2, False),
-                                          (4, 77, 2, True), (2, 300, 2, True), (2, 256, 1, False)])
+                                          (4, 77, 2, True), (2, 300, 2, True), (2, 256, 1, False),
+                                          # more (clip, head, K/V tile) items than SMs: the persistent backward walks several
+                                          # items per CTA (causal: a different number of query tiles per item)
+                                          (16, 300, 6, False), (20, 400, 4, True), (40, 77, 8, True)])
 def test_attention_fwd_bwd(ops, B, S, H, causal):
     qkv = rnd(B, S, 3 * H * 64, seed=11)
     scale = 0.125
