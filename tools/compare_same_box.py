@@ -153,7 +153,7 @@ def gemm_rows(quick):
     pre = y1
     dxh = torch.empty(M, Hd, dtype=bf16, device=DEV)
     add("gemm NN dfc2  [M,768]x[768,3072] * gelu'", lambda: ops.linear_dgrad(x, w2, ops.EPI_DGELU, pre=pre, out=dxh),
-        lambda: torch.matmul(x, w2) * pre, 2.0 * M * Hd * D)
+        lambda: torch.ops.aten.gelu_backward(torch.matmul(x, w2), pre), 2.0 * M * Hd * D)      # pre = the bf16 pre-activation
     # ---- wgrad (TN), fp32 accumulate into the master gradient
     dwq = torch.zeros(3 * D, D, device=DEV)
     add("gemm TN wqkv  [2304,M]x[M,768] -> fp32 +=", lambda: ops.linear_wgrad(dyq, x, dwq), lambda: dwq.add_(torch.matmul(dyq.t(), x)), 2.0 * M * 3 * D * D)
