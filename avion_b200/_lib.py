@@ -35,6 +35,7 @@ SIGNATURES = {
     "avn_layernorm_fwd": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i, _f, _vp],
     "avn_layernorm_bwd": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i, _vp],
     "avn_gemm_bf16": [C.POINTER(GemmDesc), _vp],
+    "avn_sizeof_gemm_desc": [],
     "avn_attn_fwd": [_vp, _vp, _vp, _i, _i, _i, _f, _i, _vp],
     "avn_attn_bwd": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _f, _i, _vp],
     "avn_cast_f32_bf16": [_vp, _vp, _i64, _vp],
@@ -68,7 +69,7 @@ SIGNATURES = {
 
 # kernels launched per C-ABI call (for the bench's gpu_launches count); default 1
 KERNELS_PER_CALL = {"avn_attn_bwd": 3, "avn_infonce_bwd": 3, "avn_infonce_bwd_static": 3, "avn_infonce_static_max_floats": 0, "avn_head_bwd": 2, "avn_pos_table_bwd": 2,
-                    "avn_token_embed_bwd": 2, "avn_sample_rrc_boxes": 0, "avn_device_check": 0, "avn_version": 0,
+                    "avn_token_embed_bwd": 2, "avn_sample_rrc_boxes": 0, "avn_device_check": 0, "avn_version": 0, "avn_sizeof_gemm_desc": 0,
                     "avn_adamw_chunk_elems": 0, "avn_mse_workspace_floats": 0, "avn_mse_fwd": 2,
                     "avn_mmr_workspace_floats": 0, "avn_mmr_fwd": 3}
 launch_count = 0
@@ -91,6 +92,9 @@ def load():
             fn.restype = _i
         lib.avn_last_error.restype = C.c_char_p
         lib.avn_last_error.argtypes = []
+        if lib.avn_sizeof_gemm_desc() != C.sizeof(GemmDesc):
+            raise RuntimeError(f"avion_b200: {LIB_PATH} was built with a {lib.avn_sizeof_gemm_desc()}-byte avn_gemm_desc, this "
+                               f"binding mirrors {C.sizeof(GemmDesc)} bytes - rebuild the library (python avion_b200/csrc/build.py)")
         _lib = lib
     return _lib
 

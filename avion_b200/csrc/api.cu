@@ -15,7 +15,9 @@ void avn_set_error(const char* fmt, ...) {
 }
 
 extern "C" const char* avn_last_error(void) { return g_err; }
-extern "C" int avn_version(void) { return 100; }
+extern "C" int avn_version(void) { return 101; }
+// binding check: a host-language mirror of avn_gemm_desc (ctypes, cgo, JNI ...) compares its own size with this one at load time
+extern "C" int avn_sizeof_gemm_desc(void) { return (int)sizeof(avn_gemm_desc); }
 
 int avn_num_sms() {
     static int sms[64] = {0};

@@ -93,6 +93,8 @@ typedef struct {
                                                       `.sum(0)` autograd runs on dY), taken from the A tiles the kernel stages anyway */
 } avn_gemm_desc;
 int avn_gemm_bf16(const avn_gemm_desc* d, avn_stream_t stream);
+/* sizeof(avn_gemm_desc) as this library was built: a binding checks its mirror of the struct against it when it loads */
+int avn_sizeof_gemm_desc(void);
 
 /* ---- V4: flash-style attention on tcgen05 (replaces flash_attn_qkvpacked_func reached from transformer.py:148, and
  * nn.MultiheadAttention with the causal mask for the text tower, transformer.py:140-146,447-453); head dim 64.

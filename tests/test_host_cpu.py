@@ -28,6 +28,8 @@ def test_library_exports_every_declared_symbol(built):
         assert hasattr(lib, name), name
     assert set(_lib.SIGNATURES) <= declared
     assert lib.avn_version() >= 100
+    import ctypes
+    assert lib.avn_sizeof_gemm_desc() == ctypes.sizeof(_lib.GemmDesc)      # the ctypes mirror matches the header's struct
 
 
 def test_rrc_sampler_matches_restatement(built):

@@ -18,7 +18,7 @@ def _header_kernels():
     src = open(os.path.join(ROOT, "include", "avion_b200.h")).read()
     names = set(re.findall(r"\bint\s+avn_(\w+)\s*\(", src))
     host_only = {"version", "device_check", "sample_rrc_boxes", "adamw_chunk_elems", "mse_workspace_floats", "mmr_workspace_floats",
-                 "infonce_static_max_floats"}
+                 "infonce_static_max_floats", "sizeof_gemm_desc"}
     return names - host_only
 
 
